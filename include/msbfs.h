@@ -1,0 +1,176 @@
+/*
+ * msbfs.h — C ABI of the B200-native multi-source-BFS engine (libmsbfs.so).
+ *
+ * The reference (/root/reference/main.cu) is a single executable with no plugin
+ * or FFI surface; this ABI is cut at the function-level seam its main() already
+ * has: device set-up (main.cu:227-228, 283-295), the loaders (92-130, 134-164),
+ * the per-query BFS + sum pair called from the scheduler loop (312-322 ->
+ * GPUMultiSourceBFS 40-73, ComputeFofU 75-89) and the result reduction
+ * (324-397).  Each entry point names the reference lines it replaces.
+ *
+ * Conventions
+ *   - plain C types only; no C++ objects or exceptions cross the boundary;
+ *   - every function returns an int status (MSBFS_OK == 0); the message for the
+ *     calling thread's last failure is msbfs_last_error();
+ *   - the opaque handle owns all device memory and streams; the caller owns every
+ *     host buffer and may free it as soon as the call returns;
+ *   - one handle per (process, device); a handle is not thread-safe, distinct
+ *     handles are independent;
+ *   - there is NO CPU fallback: with no usable CUDA device msbfs_create fails.
+ */
+#ifndef MSBFS_H
+#define MSBFS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSBFS_OK          0
+#define MSBFS_ERR_INVALID 1 /* bad argument / call order                      */
+#define MSBFS_ERR_IO      2 /* file cannot be opened or is truncated          */
+#define MSBFS_ERR_CUDA    3 /* CUDA runtime failure (no device, OOM, fault)   */
+#define MSBFS_ERR_FORMAT  4 /* vertex id outside [0, n) in an edge record     */
+#define MSBFS_ERR_NOMEM   5 /* host allocation failed                         */
+#define MSBFS_ERR_RANGE   6 /* value does not fit the packed representation   */
+
+typedef struct msbfs_handle msbfs_t;
+
+/* Message describing the last failure on the calling thread ("" if none). */
+const char* msbfs_last_error(void);
+
+/* ------------------------------------------------------------ life cycle -- */
+
+/* Replaces cudaSetDevice(rank % numGPU) and the device allocations,
+ * main.cu:227-228, 283-295.  Binds the handle to `device`, creates its stream. */
+int msbfs_create(int device, msbfs_t** out);
+
+/* Replaces the cudaFree calls, main.cu:416-418. */
+int msbfs_destroy(msbfs_t* h);
+
+/* Tuning / test knobs; unknown keys -> MSBFS_ERR_INVALID.
+ *   "lanes"      0 = auto (64/128/256 by group count), or 64 / 128 / 256
+ *   "direction"  0 = direction-optimizing, 1 = top-down only, 2 = bottom-up only
+ *   "alpha"      top-down is chosen while frontier_entries * alpha < unexplored_entries
+ *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off */
+int msbfs_set_option(msbfs_t* h, const char* key, int64_t value);
+
+/* ----------------------------------------------------------------- graph -- */
+
+/* Replaces LoadGraphBin + the CSR upload, main.cu:92-130 and 283-291.
+ * File layout (main.cu:101-116): int32 n, int64 m, m x (int32 u, int32 v); every
+ * record is an undirected edge stored in both directions, duplicates and
+ * self-loops kept.  The file is streamed through pinned staging buffers with
+ * asynchronous H2D copies and the CSR (64-bit offsets) is built on the device.
+ * Unlike the reference (UB, main.cu:114-115) ids outside [0, n) are rejected
+ * with MSBFS_ERR_FORMAT.  A file that cannot be opened gives MSBFS_ERR_IO. */
+int msbfs_load_graph_file(msbfs_t* h, const char* path, int32_t* n_out, int64_t* m_out);
+
+/* Same, from `m` (u, v) records already in host memory. */
+int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int32_t* uv_pairs);
+
+/* Same, from records already resident in this handle's device memory
+ * (e.g. produced by msbfs_gen_edges_device). The buffer is only read. */
+int msbfs_set_graph_edges_device(msbfs_t* h, int32_t n, int64_t m, const int32_t* d_uv_pairs);
+
+/* --------------------------------------------------------------- queries -- */
+
+/* Replaces the scheduler loop body, main.cu:312-322 (GPUMultiSourceBFS 40-73 +
+ * ComputeFofU 75-89), for `num_groups` groups at once.  Group i's sources are
+ * sources[group_offsets[i] .. group_offsets[i+1]) (host arrays; offsets need not
+ * start at 0).  out_sums[i] = F(group i) = sum over reachable vertices of the hop
+ * distance to the nearest valid source; ids outside [0, n) are ignored
+ * (main.cu:49); unreachable vertices add nothing (main.cu:84-85); a group with no
+ * valid source gives 0.  Copies queries H2D and sums D2H inside the call. */
+int msbfs_run(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets,
+              const int32_t* sources, int64_t* out_sums);
+
+/* The same work split in three so that the traversal can be timed with inputs
+ * and outputs resident in HBM: upload (H2D), run (device only), download (D2H). */
+int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets,
+                         const int32_t* sources);
+int msbfs_run_resident(msbfs_t* h);
+int msbfs_download_sums(msbfs_t* h, int64_t* out_sums, int32_t count);
+
+/* Measurement metadata, not part of the reference's output: for the groups of the
+ * last run, the number of CSR entries of reached vertices (Graph500 traversed
+ * edges = half of it).  Runs an extra device pass when called. */
+int msbfs_reached_entries(msbfs_t* h, int64_t* out_entries, int32_t count);
+
+/* ------------------------------------------------------------- reduction -- */
+
+/* Replaces the argmin, main.cu:379-397, over a full array: first F >= 0 seeds,
+ * strict '<' keeps the lowest index among ties; K = 0 gives (-1, -1).  The report
+ * prints min_k + 1 (main.cu:409).  Host-only. */
+int msbfs_argmin(int32_t num_groups, const int64_t* sums, int32_t* min_k_out, int64_t* min_f_out);
+
+/* Local part of the distributed argmin that replaces the (q, F) Pair gather,
+ * main.cu:166-193, 324-375: packed = (F << 24) | global_query_id, minimised over
+ * sums[0..count) with ids first_qid, first_qid + 1, ...; UINT64_MAX when count = 0.
+ * A plain unsigned min over ranks then reproduces the lowest-index tie-break.
+ * MSBFS_ERR_RANGE when an id needs more than 24 bits or a sum more than 39. */
+int msbfs_argmin_packed(const int64_t* sums, int32_t first_qid, int32_t count, uint64_t* packed_out);
+int msbfs_unpack_argmin(uint64_t packed, int32_t* min_k_out, int64_t* min_f_out);
+
+/* One 8-byte min all-reduce over NCCL (replaces MPI_Gather + MPI_Gatherv,
+ * main.cu:340-365) when every rank owns its own GPU.  `nccl_comm` is an
+ * ncclComm_t; NCCL is resolved at run time (dlopen) so the library itself has no
+ * NCCL link dependency.  With several ranks on one device use MPI_Allreduce on
+ * the packed word instead. */
+int msbfs_allreduce_min_u64(msbfs_t* h, void* nccl_comm, uint64_t* inout);
+
+/* ------------------------------------------------------------ statistics -- */
+
+typedef struct msbfs_stats {
+    int32_t n;                 /* vertices in the file                              */
+    int32_t n_active;          /* vertices with degree > 0 (relabelled to the front) */
+    int64_t m;                 /* edge records                                      */
+    int64_t csr_entries;       /* 2 m                                               */
+    int32_t lanes;             /* query groups advanced together in the last run    */
+    int32_t batches;           /* lane batches in the last run                      */
+    int64_t levels;            /* BFS levels over all batches                       */
+    int64_t levels_top_down;
+    int64_t levels_bottom_up;
+    int64_t scanned_top_down;  /* CSR entries scanned by top-down kernels           */
+    int64_t scanned_bottom_up; /* CSR entries scanned by bottom-up kernels          */
+    int64_t frontier_vertices; /* sum over levels of vertices with a non-empty frontier word */
+    int64_t candidate_vertices;/* sum over bottom-up levels of vertices examined    */
+    int64_t alg_bytes;         /* algorithmic bytes of the last run     */
+    int64_t kernel_launches;   /* kernels of this library launched by the last run  */
+    double  build_ms;          /* device time of the last graph build               */
+    double  run_ms;            /* device time of the last run (CUDA events)         */
+    double  bottom_up_ms;      /* of which bottom-up kernels (if profiling enabled) */
+} msbfs_stats;
+
+int msbfs_get_stats(msbfs_t* h, msbfs_stats* out);
+
+/* ----------------------------------------------- host-side file helpers -- */
+
+/* Replaces LoadQueryBin, main.cu:134-164: uint8 K, then per group uint8 S + S x
+ * int32.  Also accepts the extended container (first byte 0, "MSBFSQ2", uint32 K,
+ * per group uint32 S + ids) needed for K or S > 255, which the reference format
+ * cannot express.  Arrays are malloc'ed; release with msbfs_free. */
+int msbfs_load_query_file(const char* path, int32_t* num_groups_out,
+                          int64_t** group_offsets_out, int32_t** sources_out);
+int msbfs_write_query_file(const char* path, int32_t num_groups, const int64_t* group_offsets,
+                           const int32_t* sources, int force_extended);
+int msbfs_write_graph_file(const char* path, int32_t n, int64_t m, const int32_t* uv_pairs);
+void msbfs_free(void* p);
+
+/* ------------------------------------------------- synthetic benchmarks -- */
+
+/* kind: 0 R-MAT (p0 = scale), 1 Kronecker = R-MAT with scrambled labels
+ * (p0 = scale), 2 lattice (p0 = width, p1 = height; m is implied), 3 Erdos-Renyi
+ * (p0 = n).  Host and device versions write identical records. */
+int msbfs_gen_num_vertices(int kind, int32_t p0, int32_t p1, int32_t* n_out);
+int msbfs_gen_edges_host(int kind, int32_t p0, int32_t p1, int64_t m, uint64_t seed, int32_t* uv_out);
+int msbfs_gen_edges_device(int device, int kind, int32_t p0, int32_t p1, int64_t m, uint64_t seed,
+                           int32_t* d_uv_out);
+int msbfs_gen_queries_host(int32_t n, int32_t num_groups, int32_t sources_per_group, uint64_t seed,
+                           int64_t* group_offsets_out, int32_t* sources_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSBFS_H */

@@ -1,0 +1,342 @@
+/*
+ * api.cu — the extern "C" entry points of include/msbfs.h that touch the GPU:
+ * handle life cycle, the streaming loader, query upload / run / download, and the
+ * NCCL min-reduction.  Reference lines replaced are cited in include/msbfs.h.
+ */
+#include "engine.h"
+
+#include <dlfcn.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <cerrno>
+#include <cstring>
+
+namespace {
+
+constexpr size_t STAGE_BYTES = 64u << 20; /* pinned staging buffer (x2) */
+
+/* Double-buffered pinned staging: while buffer i is in flight to the device the
+ * host fills buffer i^1 (from the file or from the caller's pageable array).
+ * Replaces the per-field fread loop and the pageable blocking cudaMemcpy of the
+ * reference (main.cu:108-116, 290-291). */
+struct Stager {
+    char* buf[2] = {nullptr, nullptr};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    bool used[2] = {false, false};
+    int cur = 0;
+    ~Stager() {
+        for (int i = 0; i < 2; ++i) {
+            if (buf[i]) cudaFreeHost(buf[i]);
+            if (done[i]) cudaEventDestroy(done[i]);
+        }
+    }
+    int init() {
+        for (int i = 0; i < 2; ++i) {
+            MSBFS_CUDA(cudaHostAlloc((void**)&buf[i], STAGE_BYTES, cudaHostAllocDefault));
+            MSBFS_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+        }
+        return MSBFS_OK;
+    }
+    /* buffer that is safe to overwrite */
+    int acquire(char** out) {
+        if (used[cur]) MSBFS_CUDA(cudaEventSynchronize(done[cur]));
+        *out = buf[cur];
+        return MSBFS_OK;
+    }
+    int submit(void* dst, size_t bytes, cudaStream_t s) {
+        MSBFS_CUDA(cudaMemcpyAsync(dst, buf[cur], bytes, cudaMemcpyHostToDevice, s));
+        MSBFS_CUDA(cudaEventRecord(done[cur], s));
+        used[cur] = true;
+        cur ^= 1;
+        return MSBFS_OK;
+    }
+};
+
+int set_device(msbfs_handle* h) {
+    MSBFS_CUDA(cudaSetDevice(h->device));
+    return MSBFS_OK;
+}
+
+int ensure_query_capacity(msbfs_handle* h, int64_t groups, int64_t sources) {
+    if (groups + 1 > h->q_cap_groups) {
+        cudaFree(h->d_q_offsets); cudaFree(h->d_sums);
+        h->d_q_offsets = nullptr; h->d_sums = nullptr; h->q_cap_groups = 0;
+        const int64_t cap = std::max<int64_t>(groups + 1, 1024);
+        MSBFS_CUDA(cudaMalloc(&h->d_q_offsets, sizeof(long long) * (size_t)cap));
+        MSBFS_CUDA(cudaMalloc(&h->d_sums, sizeof(long long) * (size_t)cap));
+        h->q_cap_groups = cap;
+    }
+    if (sources > h->q_cap_sources) {
+        cudaFree(h->d_q_sources);
+        h->d_q_sources = nullptr; h->q_cap_sources = 0;
+        const int64_t cap = std::max<int64_t>(sources, 4096);
+        MSBFS_CUDA(cudaMalloc(&h->d_q_sources, sizeof(int) * (size_t)cap));
+        h->q_cap_sources = cap;
+    }
+    const size_t need = sizeof(long long) * (size_t)(groups + 1) + sizeof(int) * (size_t)std::max<int64_t>(sources, 1)
+                        + sizeof(long long) * (size_t)std::max<int64_t>(groups, 1);
+    if (need > h->h_pinned_io_bytes) {
+        if (h->h_pinned_io) cudaFreeHost(h->h_pinned_io);
+        h->h_pinned_io = nullptr; h->h_pinned_io_bytes = 0;
+        const size_t cap = std::max<size_t>(need, 1u << 20);
+        MSBFS_CUDA(cudaHostAlloc((void**)&h->h_pinned_io, cap, cudaHostAllocDefault));
+        h->h_pinned_io_bytes = cap;
+    }
+    return MSBFS_OK;
+}
+
+} // namespace
+
+extern "C" int msbfs_create(int device, msbfs_t** out) {
+    if (!out) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_create: null output pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return msbfs_fail(MSBFS_ERR_CUDA, "no CUDA device available (%s); this engine has no CPU fallback",
+                          e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count)
+        return msbfs_fail(MSBFS_ERR_INVALID, "device %d out of range [0, %d)", device, count);
+    MSBFS_CUDA(cudaSetDevice(device));
+    msbfs_handle* h = new (std::nothrow) msbfs_handle();
+    if (!h) return msbfs_fail(MSBFS_ERR_NOMEM, "out of host memory");
+    h->device = device;
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (h->sm_count <= 0) h->sm_count = 148;
+    e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete h;
+        return msbfs_fail(MSBFS_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+    }
+    std::memset(&h->stats, 0, sizeof h->stats);
+    *out = h;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_destroy(msbfs_t* h) {
+    if (!h) return MSBFS_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    msbfs_release_traversal(h);
+    msbfs_release_graph(h);
+    cudaFree(h->d_q_offsets); cudaFree(h->d_q_sources); cudaFree(h->d_sums); cudaFree(h->d_scalar);
+    if (h->h_pinned_io) cudaFreeHost(h->h_pinned_io);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
+    if (!h || !key) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_option: null argument");
+    if (!std::strcmp(key, "lanes")) {
+        if (value != 0 && value != 64 && value != 128 && value != 256)
+            return msbfs_fail(MSBFS_ERR_INVALID, "lanes must be 0, 64, 128 or 256");
+        h->opt_lanes = (int)value;
+    } else if (!std::strcmp(key, "direction")) {
+        if (value < 0 || value > 2) return msbfs_fail(MSBFS_ERR_INVALID, "direction must be 0, 1 or 2");
+        h->opt_direction = (int)value;
+    } else if (!std::strcmp(key, "alpha")) {
+        if (value < 1) return msbfs_fail(MSBFS_ERR_INVALID, "alpha must be >= 1");
+        h->opt_alpha = value;
+    } else if (!std::strcmp(key, "l2_persist")) {
+        h->opt_l2_persist = value != 0;
+    } else {
+        return msbfs_fail(MSBFS_ERR_INVALID, "unknown option '%s'", key);
+    }
+    return MSBFS_OK;
+}
+
+/* ----------------------------------------------------------------- graph --- */
+
+extern "C" int msbfs_set_graph_edges_device(msbfs_t* h, int32_t n, int64_t m, const int32_t* d_uv_pairs) {
+    if (!h || n < 0 || m < 0 || (m > 0 && !d_uv_pairs))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_graph_edges_device: bad argument");
+    int rc = set_device(h);
+    if (rc) return rc;
+    /* the caller's buffer may have been written on another stream */
+    MSBFS_CUDA(cudaDeviceSynchronize());
+    return msbfs_build_from_device_edges(h, n, m, d_uv_pairs);
+}
+
+extern "C" int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int32_t* uv_pairs) {
+    if (!h || n < 0 || m < 0 || (m > 0 && !uv_pairs))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_graph_edges: bad argument");
+    int rc = set_device(h);
+    if (rc) return rc;
+    int32_t* d_uv = nullptr;
+    const size_t total = sizeof(int32_t) * 2 * (size_t)m;
+    MSBFS_CUDA(cudaMalloc(&d_uv, std::max<size_t>(total, 8)));
+    Stager st;
+    rc = st.init();
+    for (size_t off = 0; rc == MSBFS_OK && off < total; off += STAGE_BYTES) {
+        const size_t len = std::min(STAGE_BYTES, total - off);
+        char* p = nullptr;
+        rc = st.acquire(&p);
+        if (rc) break;
+        std::memcpy(p, reinterpret_cast<const char*>(uv_pairs) + off, len);
+        rc = st.submit(reinterpret_cast<char*>(d_uv) + off, len, h->stream);
+    }
+    if (rc == MSBFS_OK && cudaStreamSynchronize(h->stream) != cudaSuccess)
+        rc = msbfs_fail(MSBFS_ERR_CUDA, "edge upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc == MSBFS_OK) rc = msbfs_build_from_device_edges(h, n, m, d_uv);
+    cudaFree(d_uv);
+    return rc;
+}
+
+extern "C" int msbfs_load_graph_file(msbfs_t* h, const char* path, int32_t* n_out, int64_t* m_out) {
+    if (!h || !path) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_load_graph_file: null argument");
+    int rc = set_device(h);
+    if (rc) return rc;
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return msbfs_fail(MSBFS_ERR_IO, "Could not open graph file %s", path); /* main.cu:95-99 */
+    struct Closer { int fd; ~Closer() { close(fd); } } closer{fd};
+    unsigned char hdr[12];
+    if (read(fd, hdr, 12) != 12) return msbfs_fail(MSBFS_ERR_IO, "graph file %s is shorter than its 12-byte header", path);
+    int32_t n; int64_t m;
+    std::memcpy(&n, hdr, 4);       /* main.cu:102 */
+    std::memcpy(&m, hdr + 4, 8);   /* main.cu:104 */
+    if (n < 0 || m < 0) return msbfs_fail(MSBFS_ERR_FORMAT, "graph file %s has a negative size field", path);
+    struct stat stt;
+    if (fstat(fd, &stt) == 0 && S_ISREG(stt.st_mode) && (int64_t)stt.st_size < 12 + 8 * m)
+        return msbfs_fail(MSBFS_ERR_IO, "graph file %s is truncated: %lld records declared, %lld bytes present", path,
+                          (long long)m, (long long)stt.st_size);
+#ifdef POSIX_FADV_SEQUENTIAL
+    posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
+    int32_t* d_uv = nullptr;
+    const size_t total = 8 * (size_t)m;
+    MSBFS_CUDA(cudaMalloc(&d_uv, std::max<size_t>(total, 8)));
+    Stager st;
+    rc = st.init();
+    for (size_t off = 0; rc == MSBFS_OK && off < total; off += STAGE_BYTES) {
+        const size_t len = std::min(STAGE_BYTES, total - off);
+        char* p = nullptr;
+        rc = st.acquire(&p);
+        if (rc) break;
+        size_t got = 0;
+        while (got < len) {
+            const ssize_t r = read(fd, p + got, len - got);
+            if (r < 0 && errno == EINTR) continue;
+            if (r <= 0) { rc = msbfs_fail(MSBFS_ERR_IO, "short read on graph file %s", path); break; }
+            got += (size_t)r;
+        }
+        if (rc) break;
+        rc = st.submit(reinterpret_cast<char*>(d_uv) + off, len, h->stream);
+    }
+    if (rc == MSBFS_OK && cudaStreamSynchronize(h->stream) != cudaSuccess)
+        rc = msbfs_fail(MSBFS_ERR_CUDA, "edge upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc == MSBFS_OK) rc = msbfs_build_from_device_edges(h, n, m, d_uv);
+    cudaFree(d_uv);
+    if (rc == MSBFS_OK) {
+        if (n_out) *n_out = n;
+        if (m_out) *m_out = m;
+    }
+    return rc;
+}
+
+/* --------------------------------------------------------------- queries --- */
+
+extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets,
+                                    const int32_t* sources) {
+    if (!h || num_groups < 0 || (num_groups > 0 && !group_offsets))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_upload_queries: bad argument");
+    int rc = set_device(h);
+    if (rc) return rc;
+    const int64_t base = num_groups > 0 ? group_offsets[0] : 0;
+    const int64_t total = num_groups > 0 ? group_offsets[num_groups] - base : 0;
+    if (total < 0 || (total > 0 && !sources)) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_upload_queries: bad offsets");
+    for (int32_t i = 0; i < num_groups; ++i)
+        if (group_offsets[i + 1] < group_offsets[i]) return msbfs_fail(MSBFS_ERR_INVALID, "group offsets must not decrease");
+    rc = ensure_query_capacity(h, num_groups, total);
+    if (rc) return rc;
+    /* stage through pinned memory so both copies are truly asynchronous */
+    long long* p_off = h->h_pinned_io;
+    int* p_src = reinterpret_cast<int*>(p_off + num_groups + 1);
+    for (int32_t i = 0; i <= num_groups; ++i) p_off[i] = num_groups > 0 ? group_offsets[i] - base : 0;
+    if (total > 0) std::memcpy(p_src, sources + base, sizeof(int) * (size_t)total);
+    MSBFS_CUDA(cudaMemcpyAsync(h->d_q_offsets, p_off, sizeof(long long) * (size_t)(num_groups + 1), cudaMemcpyHostToDevice, h->stream));
+    if (total > 0)
+        MSBFS_CUDA(cudaMemcpyAsync(h->d_q_sources, p_src, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, h->stream));
+    MSBFS_CUDA(cudaStreamSynchronize(h->stream));
+    h->q_groups = num_groups;
+    h->q_sources = total;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_run_resident(msbfs_t* h) {
+    if (!h) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_run_resident: null handle");
+    int rc = set_device(h);
+    if (rc) return rc;
+    return msbfs_traverse(h);
+}
+
+extern "C" int msbfs_download_sums(msbfs_t* h, int64_t* out_sums, int32_t count) {
+    if (!h || count < 0 || (count > 0 && !out_sums)) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_download_sums: bad argument");
+    if (count > h->q_groups) return msbfs_fail(MSBFS_ERR_INVALID, "only %d sums are resident", h->q_groups);
+    if (count == 0) return MSBFS_OK;
+    int rc = set_device(h);
+    if (rc) return rc;
+    long long* p = h->h_pinned_io;
+    MSBFS_CUDA(cudaMemcpyAsync(p, h->d_sums, sizeof(long long) * (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    MSBFS_CUDA(cudaStreamSynchronize(h->stream));
+    std::memcpy(out_sums, p, sizeof(long long) * (size_t)count);
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_run(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets, const int32_t* sources,
+                         int64_t* out_sums) {
+    if (!h) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_run: null handle");
+    if (!h->has_graph) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_run: no graph loaded");
+    if (num_groups > 0 && !out_sums) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_run: null output");
+    int rc = msbfs_upload_queries(h, num_groups, group_offsets, sources);
+    if (rc) return rc;
+    rc = msbfs_run_resident(h);
+    if (rc) return rc;
+    return msbfs_download_sums(h, out_sums, num_groups);
+}
+
+extern "C" int msbfs_reached_entries(msbfs_t* h, int64_t* out_entries, int32_t count) {
+    if (!h || count < 0 || (count > 0 && !out_entries)) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_reached_entries: bad argument");
+    if (count > h->q_groups) return msbfs_fail(MSBFS_ERR_INVALID, "only %d groups are resident", h->q_groups);
+    int rc = set_device(h);
+    if (rc) return rc;
+    return msbfs_reached_entries_impl(h, out_entries, count);
+}
+
+extern "C" int msbfs_get_stats(msbfs_t* h, msbfs_stats* out) {
+    if (!h || !out) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_stats: null argument");
+    h->stats.n = h->n; h->stats.n_active = h->n_active; h->stats.m = h->m; h->stats.csr_entries = h->nnz;
+    h->stats.build_ms = h->build_ms;
+    *out = h->stats;
+    return MSBFS_OK;
+}
+
+/* ------------------------------------------------------------- reduction --- */
+
+extern "C" int msbfs_allreduce_min_u64(msbfs_t* h, void* nccl_comm, uint64_t* inout) {
+    if (!h || !nccl_comm || !inout) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_allreduce_min_u64: null argument");
+    typedef int (*allreduce_fn)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+    static allreduce_fn fn = nullptr;
+    if (!fn) {
+        void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD); /* reuse a copy the process already has */
+        if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW);
+        if (!lib) return msbfs_fail(MSBFS_ERR_INVALID, "NCCL not found: %s", dlerror());
+        fn = (allreduce_fn)dlsym(lib, "ncclAllReduce");
+        if (!fn) return msbfs_fail(MSBFS_ERR_INVALID, "ncclAllReduce not found in libnccl");
+    }
+    int rc = set_device(h);
+    if (rc) return rc;
+    if (!h->d_scalar) MSBFS_CUDA(cudaMalloc(&h->d_scalar, 8));
+    uint64_t* d = reinterpret_cast<uint64_t*>(h->d_scalar);
+    MSBFS_CUDA(cudaMemcpyAsync(d, inout, 8, cudaMemcpyHostToDevice, h->stream));
+    const int ncclUint64 = 5, ncclMin = 3; /* nccl.h: ncclDataType_t / ncclRedOp_t */
+    const int nrc = fn(d, d, 1, ncclUint64, ncclMin, nccl_comm, h->stream);
+    if (nrc != 0) return msbfs_fail(MSBFS_ERR_CUDA, "ncclAllReduce failed with code %d", nrc);
+    MSBFS_CUDA(cudaMemcpyAsync(inout, d, 8, cudaMemcpyDeviceToHost, h->stream));
+    MSBFS_CUDA(cudaStreamSynchronize(h->stream));
+    return MSBFS_OK;
+}

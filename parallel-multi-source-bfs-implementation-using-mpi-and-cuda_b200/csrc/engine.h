@@ -1,0 +1,155 @@
+/*
+ * engine.h — internal layout of an msbfs handle and the launch interfaces between
+ * the translation units of libmsbfs.so.  Not part of the C ABI.
+ *
+ * Data layout in HBM (all owned by the handle):
+ *   perm      int32 [n]            file vertex id -> internal id.  Internal ids are
+ *                                  sorted by degree, descending; isolated vertices
+ *                                  get ids >= n_active and take no further part.
+ *   row_ptr   int64 [n_pad + 1]    CSR offsets over internal ids (64-bit: 2m can
+ *                                  exceed 2^31, unlike main.cu:119-124)
+ *   col       int32 [2m]           neighbours (internal ids), each row sorted
+ *                                  ascending = highest-degree neighbour first
+ *   visited / cur / nxt / acc      lane words, n_pad x NW x uint64.  Bit j of a
+ *                                  vertex's word belongs to query group (lane) j of
+ *                                  the running batch.  NW = 1, 2 or 4 (64/128/256
+ *                                  lanes); at NW = 4 a word is one 32-byte sector
+ *                                  and moves as a single LDG/STG.256.
+ *   cur_nz / nxt_nz / vis_full     bitmaps, one bit per vertex: frontier word is
+ *                                  non-zero / all batch lanes have visited it.  A
+ *                                  cur/nxt word is only meaningful when its bit is
+ *                                  set, so the word arrays are never cleared.
+ *   hub_acc                        lane words for the heavy (chunked) vertices,
+ *                                  all-zero between kernels.
+ *   ctrl                           per-batch control block (counts, sums, live
+ *                                  lanes, direction decision) — the level loop's
+ *                                  state lives on the device; the host only reads
+ *                                  a 32-byte verdict per level.
+ */
+#ifndef MSBFS_ENGINE_H
+#define MSBFS_ENGINE_H
+
+#include "internal.h"
+
+#include <cstdint>
+#include <vector>
+
+constexpr int MSBFS_MAX_NW      = 4;     /* 256 lanes */
+constexpr int MSBFS_MAX_LANES   = 64 * MSBFS_MAX_NW;
+constexpr int MSBFS_CHUNK       = 1024;  /* CSR entries per heavy-row chunk (one warp) */
+constexpr int MSBFS_DEG_HEAVY   = 1024;  /* deg >= this: row is split into chunks      */
+constexpr int MSBFS_DEG_WARP    = 64;    /* deg >  this: one warp per vertex           */
+constexpr int MSBFS_DEG_G8      = 8;     /* deg >  this: 8 threads per vertex, else 2  */
+
+/* per-level record kept on the device and copied back after a run */
+struct LevelLog {
+    int32_t  level;        /* BFS depth that was expanded                */
+    int32_t  direction;    /* 1 top-down, 2 bottom-up, 0 source injection */
+    uint64_t frontier_vertices;   /* vertices with a non-empty NEW frontier word */
+    uint64_t frontier_entries;    /* their CSR entries                           */
+    int64_t  unexplored_entries;  /* CSR entries of vertices not yet full         */
+    uint64_t scanned;             /* CSR entries scanned by this level            */
+    uint64_t words_fetched;       /* lane words fetched through col (random)      */
+    uint64_t vertices_examined;   /* candidates (BU) / expanded vertices (TD)     */
+    uint64_t words_written;       /* lane words stored or OR-ed                   */
+};
+
+struct LevelCtrl {
+    unsigned long long cnt[MSBFS_MAX_LANES];   /* newly visited vertices per lane, this level */
+    unsigned long long sums[MSBFS_MAX_LANES];  /* running distance sums per lane              */
+    unsigned long long live[MSBFS_MAX_NW];     /* lanes whose frontier is non-empty           */
+    unsigned long long active[MSBFS_MAX_NW];   /* lanes that carry a query group              */
+    unsigned long long n_f, m_f;               /* new frontier: vertices, CSR entries         */
+    long long          m_u;                    /* CSR entries of not-yet-full vertices        */
+    unsigned long long scanned, words_fetched, examined, words_written; /* this level        */
+    int level;                                 /* depth being expanded (-1 = injection)       */
+    int log_pos;
+};
+
+/* what the host reads back after each level (pinned, written by the epilogue) */
+struct LevelVerdict {
+    int32_t done;
+    int32_t next_direction;
+    uint64_t n_f, m_f;
+    int64_t m_u;
+};
+
+struct TravArgs {
+    const long long* row_ptr;
+    const int*       col;
+    unsigned long long* visited;
+    unsigned long long* cur;
+    unsigned long long* nxt;
+    unsigned long long* acc;
+    unsigned long long* hub_acc;
+    unsigned int* cur_nz;
+    unsigned int* nxt_nz;
+    unsigned int* vis_full;
+    LevelCtrl* ctrl;
+    const long long* chunk_level_base; /* [n_chunk_levels + 1] */
+    int n_chunk_levels;
+    long long n_chunks;
+    int n_pad;      /* vertices incl. padding to a multiple of 32 */
+    int blk_heavy;  /* 32-vertex blocks [0, blk_heavy)        : chunked rows    */
+    int blk_warp;   /*                 [blk_heavy, blk_warp)  : warp per vertex */
+    int blk_g8;     /*                 [blk_warp, blk_g8)     : 8 threads/vertex */
+    int blk_end;    /*                 [blk_g8, blk_end)      : 2 threads/vertex */
+};
+
+struct msbfs_handle {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+
+    /* graph */
+    int32_t n = 0, n_active = 0, n_pad = 0;
+    int64_t m = 0, nnz = 0;
+    int32_t* d_perm = nullptr;
+    long long* d_row_ptr = nullptr;
+    int* d_col = nullptr;
+    int blk_heavy = 0, blk_warp = 0, blk_g8 = 0, blk_end = 0;
+    long long* d_chunk_level_base = nullptr;
+    int n_chunk_levels = 0;
+    long long n_chunks = 0;
+    bool has_graph = false;
+    double build_ms = 0.0;
+
+    /* traversal state */
+    int nw_alloc = 0;
+    unsigned long long *d_visited = nullptr, *d_cur = nullptr, *d_nxt = nullptr, *d_acc = nullptr, *d_hub_acc = nullptr;
+    unsigned int *d_bitmaps = nullptr; /* cur_nz | nxt_nz | vis_full, contiguous (one L2 window) */
+    LevelCtrl* d_ctrl = nullptr;
+    LevelLog* d_log = nullptr;
+    int log_cap = 0;
+    LevelVerdict* h_verdict = nullptr; /* pinned */
+
+    /* resident queries / results */
+    int32_t q_groups = 0;
+    int64_t q_sources = 0;
+    long long* d_q_offsets = nullptr;
+    int* d_q_sources = nullptr;
+    long long* d_sums = nullptr;
+    int64_t q_cap_groups = 0, q_cap_sources = 0;
+    long long* h_pinned_io = nullptr; /* pinned staging for queries in / sums out */
+    size_t h_pinned_io_bytes = 0;
+    unsigned long long* d_scalar = nullptr; /* 8-byte scratch for the packed min all-reduce */
+
+    /* options */
+    int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
+    long long opt_alpha = 8;
+
+    /* stats of the last run */
+    msbfs_stats stats{};
+    std::vector<LevelLog> level_log;
+};
+
+/* graph_build.cu */
+int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const int32_t* d_uv);
+void msbfs_release_graph(msbfs_handle* h);
+
+/* traverse.cu */
+int msbfs_traverse(msbfs_handle* h);
+int msbfs_reached_entries_impl(msbfs_handle* h, int64_t* out_entries, int32_t count);
+void msbfs_release_traversal(msbfs_handle* h);
+
+#endif

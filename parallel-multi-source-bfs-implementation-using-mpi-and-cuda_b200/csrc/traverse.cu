@@ -1,0 +1,928 @@
+/*
+ * traverse.cu — the bit-parallel, direction-optimizing multi-source BFS kernels
+ * (sm_100a) and the level loop that drives them.
+ *
+ * Replaces, for a whole batch of query groups at once, what the reference does one
+ * group at a time: GPUMultiSourceBFS (/root/reference/main.cu:40-73, one launch of
+ * BFSKernal main.cu:16-38 and three blocking runtime calls per BFS level) and
+ * ComputeFofU (main.cu:75-89, a D2H copy of all distances and a serial host sum).
+ *
+ * Up to 256 query groups ("lanes") advance together.  Per vertex, bit j of a lane
+ * word says something about group j: visited, in the current frontier, in the next
+ * frontier.  A BFS level is then, for every vertex, an OR over neighbours' frontier
+ * words; one pass over the CSR serves all lanes.  Distances are never stored: a
+ * vertex first reached by lane j while level L is expanded adds (L + 1) to F(j), so
+ * F(j) = sum over levels of (L + 1) x (vertices newly reached by j), which is
+ * exactly the reference's sum over non-negative distances (main.cu:81-87);
+ * unreachable vertices add nothing (main.cu:84-85) and ids outside [0, n) never
+ * enter a frontier (main.cu:49).
+ *
+ * Kernels (NW = 64-bit words per lane word; G = threads cooperating on one vertex):
+ *   inject      sources -> acc words + touched bitmap
+ *   td_expand   top-down: frontier vertices push their word to neighbours (RED.OR)
+ *   td_heavy    same for chunked hub rows
+ *   td_finalize acc -> new frontier word, visited |= new
+ *   bu_sweep    bottom-up: every not-yet-full vertex ORs its neighbours' frontier
+ *               words, stops as soon as all live lanes are found; fused finalize
+ *   bu_heavy    same for hub rows, one warp per 1024-entry chunk, chunks of a row
+ *               co-operate through hub_acc
+ *   bu_heavy_finalize
+ *   count       positional popcount of the new frontier words (per-lane counts)
+ *               with bit-sliced carry-save counters and warp bit-matrix transposes
+ *   epilogue    F += (L+1) x counts, live-lane mask, direction for the next level
+ */
+#include "engine.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace {
+
+typedef unsigned long long ull;
+
+constexpr int CTA = 256;
+
+/* ------------------------------------------------------------ lane words --- */
+
+template <int NW> struct alignas(8 * NW) LW { ull w[NW]; };
+
+template <int NW> __device__ __forceinline__ LW<NW> lw_zero() {
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = 0ull;
+    return r;
+}
+template <int NW> __device__ __forceinline__ bool lw_any(const LW<NW>& a) {
+    ull r = 0ull;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r |= a.w[i];
+    return r != 0ull;
+}
+template <int NW> __device__ __forceinline__ LW<NW> lw_or(const LW<NW>& a, const LW<NW>& b) {
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = a.w[i] | b.w[i];
+    return r;
+}
+template <int NW> __device__ __forceinline__ LW<NW> lw_and(const LW<NW>& a, const LW<NW>& b) {
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = a.w[i] & b.w[i];
+    return r;
+}
+template <int NW> __device__ __forceinline__ LW<NW> lw_andn(const LW<NW>& a, const LW<NW>& b) { /* a & ~b */
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = a.w[i] & ~b.w[i];
+    return r;
+}
+/* (a & b) == b : every bit of b is present in a */
+template <int NW> __device__ __forceinline__ bool lw_covers(const LW<NW>& a, const LW<NW>& b) {
+    ull r = 0ull;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r |= (b.w[i] & ~a.w[i]);
+    return r == 0ull;
+}
+/* at NW = 4 these compile to one LDG.E.256 / STG.E.256 (32-byte sector) */
+template <int NW> __device__ __forceinline__ LW<NW> lw_load(const ull* base, long long idx) {
+    return *reinterpret_cast<const LW<NW>*>(base + idx * NW);
+}
+template <int NW> __device__ __forceinline__ LW<NW> lw_load_volatile(const ull* base, long long idx) {
+    LW<NW> r;
+    const volatile ull* p = base + idx * NW;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = p[i];
+    return r;
+}
+template <int NW> __device__ __forceinline__ void lw_store(ull* base, long long idx, const LW<NW>& v) {
+    *reinterpret_cast<LW<NW>*>(base + idx * NW) = v;
+}
+template <int NW> __device__ __forceinline__ LW<NW> lw_from(const ull* p) {
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) r.w[i] = p[i];
+    return r;
+}
+
+/* OR across the G threads named in gmask (redux.sync) */
+template <int NW, int G> __device__ __forceinline__ LW<NW> group_or(const LW<NW>& a, unsigned gmask) {
+    if (G == 1) return a;
+    LW<NW> r;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+        unsigned lo = (unsigned)a.w[i], hi = (unsigned)(a.w[i] >> 32);
+        lo = __reduce_or_sync(gmask, lo);
+        hi = __reduce_or_sync(gmask, hi);
+        r.w[i] = ((ull)hi << 32) | lo;
+    }
+    return r;
+}
+
+__device__ __forceinline__ ull warp_sum(ull v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+__device__ __forceinline__ bool test_bit(const unsigned* bitmap, int v) {
+    return (bitmap[v >> 5] >> (v & 31)) & 1u;
+}
+
+/* warps of a launch walk 32-vertex blocks with this stride */
+__device__ __forceinline__ int global_warp() { return (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5); }
+__device__ __forceinline__ int total_warps() { return (int)((gridDim.x * blockDim.x) >> 5); }
+
+/* ---------------------------------------------------------------- inject --- */
+
+/* Sources of the batch's groups become bits in acc (all-zero on entry) and in the
+ * touched bitmap; td_finalize then turns them into the level-0 frontier.  Ids
+ * outside [0, n) are dropped (main.cu:49); isolated sources reach nothing and add
+ * 0 to F, so they are dropped as well. */
+template <int NW>
+__global__ void __launch_bounds__(CTA) inject_kernel(TravArgs a, const int* __restrict__ perm, int n, int n_active,
+                                                     const long long* __restrict__ q_off, const int* __restrict__ q_src,
+                                                     int group_base, int lanes) {
+    const int g = global_warp();
+    const int lane = threadIdx.x & 31;
+    if (g >= lanes) return;
+    const long long beg = q_off[group_base + g], end = q_off[group_base + g + 1];
+    for (long long i = beg + lane; i < end; i += 32) {
+        const int s = q_src[i];
+        if ((unsigned)s >= (unsigned)n) continue;
+        const int v = perm[s];
+        if (v >= n_active) continue;
+        atomicOr(&a.acc[(long long)v * NW + (g >> 6)], 1ull << (g & 63));
+        atomicOr(&a.nxt_nz[v >> 5], 1u << (v & 31));
+    }
+}
+
+/* ------------------------------------------------------------- top-down --- */
+
+/* One frontier vertex v pushes cur[v] to every neighbour u that still misses some
+ * of those lanes.  U entries are staged per thread: U independent col loads, then U
+ * bitmap tests, then U visited-word loads, so a thread keeps up to U random
+ * requests in flight. */
+template <int NW, int U>
+__device__ __forceinline__ void td_push(const TravArgs& a, const LW<NW>& f, long long e, long long end, int stride,
+                                        ull& scanned, ull& fetched, ull& written) {
+    for (; e < end; e += (long long)stride * U) {
+        int u[U];
+        bool ok[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            const long long ee = e + (long long)k * stride;
+            ok[k] = ee < end;
+            u[k] = ok[k] ? __ldg(a.col + ee) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            scanned += ok[k];
+            ok[k] = ok[k] && !test_bit(a.vis_full, u[k]);
+        }
+        LW<NW> vis[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) vis[k] = ok[k] ? lw_load<NW>(a.visited, u[k]) : lw_zero<NW>();
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            if (!ok[k]) continue;
+            ++fetched;
+            const LW<NW> d = lw_andn(f, vis[k]);
+            if (!lw_any(d)) continue;
+#pragma unroll
+            for (int i = 0; i < NW; ++i)
+                if (d.w[i]) atomicOr(&a.acc[(long long)u[k] * NW + i], d.w[i]);
+            ++written;
+            if (!test_bit(a.nxt_nz, u[k])) atomicOr(&a.nxt_nz[u[k] >> 5], 1u << (u[k] & 31));
+        }
+    }
+}
+
+__device__ __forceinline__ void flush_counters(LevelCtrl* c, ull scanned, ull fetched, ull examined, ull written) {
+    scanned = warp_sum(scanned);
+    fetched = warp_sum(fetched);
+    examined = warp_sum(examined);
+    written = warp_sum(written);
+    if ((threadIdx.x & 31) == 0) {
+        if (scanned) atomicAdd(&c->scanned, scanned);
+        if (fetched) atomicAdd(&c->words_fetched, fetched);
+        if (examined) atomicAdd(&c->examined, examined);
+        if (written) atomicAdd(&c->words_written, written);
+    }
+}
+
+template <int NW, int G, int U>
+__global__ void __launch_bounds__(CTA) td_expand_kernel(TravArgs a, int blk_lo, int blk_hi) {
+    constexpr int VPI = 32 / G; /* frontier vertices handled per pass of the warp */
+    const int lane = threadIdx.x & 31;
+    const int sub = lane % G, grp = lane / G;
+    ull scanned = 0, fetched = 0, examined = 0, written = 0;
+    for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
+        const unsigned w = a.cur_nz[b];
+        if (w == 0u) continue;
+        const int nset = __popc(w);
+        for (int k0 = 0; k0 < nset; k0 += VPI) {
+            const int k = k0 + grp;
+            if (k >= nset) continue;
+            const int v = (b << 5) + (int)__fns(w, 0, k + 1);
+            const LW<NW> f = lw_load<NW>(a.cur, v);
+            const long long beg = a.row_ptr[v], end = a.row_ptr[v + 1];
+            if (sub == 0) ++examined;
+            td_push<NW, U>(a, f, beg + sub, end, G, scanned, fetched, written);
+        }
+    }
+    flush_counters(a.ctrl, scanned, fetched, examined, written);
+}
+
+/* chunk id -> (level k, vertex): level k holds vertices [0, base[k+1]-base[k]) */
+__device__ __forceinline__ void chunk_lookup(const TravArgs& a, long long c, int& k_out, int& v_out) {
+    int lo = 0, hi = a.n_chunk_levels; /* largest k with base[k] <= c */
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (a.chunk_level_base[mid] <= c) lo = mid; else hi = mid;
+    }
+    k_out = lo;
+    v_out = (int)(c - a.chunk_level_base[lo]);
+}
+
+template <int NW, int U>
+__global__ void __launch_bounds__(CTA) td_heavy_kernel(TravArgs a) {
+    const int lane = threadIdx.x & 31;
+    ull scanned = 0, fetched = 0, examined = 0, written = 0;
+    for (long long c = global_warp(); c < a.n_chunks; c += total_warps()) {
+        int k, v;
+        chunk_lookup(a, c, k, v);
+        if (!test_bit(a.cur_nz, v)) continue;
+        const LW<NW> f = lw_load<NW>(a.cur, v);
+        const long long beg = a.row_ptr[v] + (long long)k * MSBFS_CHUNK;
+        const long long end = min(beg + (long long)MSBFS_CHUNK, a.row_ptr[v + 1]);
+        if (lane == 0 && k == 0) ++examined;
+        td_push<NW, U>(a, f, beg + lane, end, 32, scanned, fetched, written);
+    }
+    flush_counters(a.ctrl, scanned, fetched, examined, written);
+}
+
+/* acc -> new frontier.  acc already excludes visited lanes (td_push masks with
+ * ~visited, and visited does not change while a level is expanded). */
+template <int NW>
+__global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) {
+    const int lane = threadIdx.x & 31;
+    const LW<NW> active = lw_from<NW>(a.ctrl->active);
+    long long mu_delta = 0;
+    for (int b = global_warp(); b < nblk; b += total_warps()) {
+        const unsigned w = a.nxt_nz[b];
+        if (w == 0u) continue;
+        bool full_now = false;
+        if ((w >> lane) & 1u) {
+            const int v = (b << 5) + lane;
+            const LW<NW> x = lw_load<NW>(a.acc, v);
+            lw_store<NW>(a.acc, v, lw_zero<NW>());
+            const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
+            lw_store<NW>(a.visited, v, nv);
+            lw_store<NW>(a.nxt, v, x);
+            if (lw_covers(nv, active)) {
+                full_now = true;
+                mu_delta -= a.row_ptr[v + 1] - a.row_ptr[v];
+            }
+        }
+        const unsigned fb = __ballot_sync(0xffffffffu, full_now);
+        if (fb && lane == 0) a.vis_full[b] |= fb;
+    }
+    mu_delta = (long long)warp_sum((ull)mu_delta);
+    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+}
+
+/* ------------------------------------------------------------ bottom-up --- */
+
+/* One outer step of a bottom-up scan: up to U entries per thread, staged so that
+ * the col loads, the frontier-bitmap tests and the frontier-word loads of the U
+ * entries are each issued back to back.  Returns the OR of the fetched words. */
+template <int NW, int U>
+__device__ __forceinline__ LW<NW> bu_gather(const TravArgs& a, bool go, long long e, long long end, int stride,
+                                            ull& scanned, ull& fetched) {
+    int v[U];
+    bool ok[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+        const long long ee = e + (long long)k * stride;
+        ok[k] = go && ee < end;
+        v[k] = ok[k] ? __ldg(a.col + ee) : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+        scanned += ok[k];
+        ok[k] = ok[k] && test_bit(a.cur_nz, v[k]);
+    }
+    LW<NW> x[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+        x[k] = ok[k] ? lw_load<NW>(a.cur, v[k]) : lw_zero<NW>();
+        fetched += ok[k];
+    }
+    LW<NW> t = x[0];
+#pragma unroll
+    for (int k = 1; k < U; ++k) t = lw_or(t, x[k]);
+    return t;
+}
+
+/* A warp owns 32 consecutive vertices and handles 32/G of them at a time, G threads
+ * per vertex.  Degrees are sorted, so the vertices of a warp have similar row
+ * lengths and the warp-uniform inner loop wastes little. */
+template <int NW, int G, int U>
+__global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, int blk_hi) {
+    constexpr int VPI = 32 / G;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane % G, grp = lane / G;
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
+    const LW<NW> live = lw_from<NW>(a.ctrl->live);
+    const LW<NW> active = lw_from<NW>(a.ctrl->active);
+    ull scanned = 0, fetched = 0, examined = 0, written = 0;
+    long long mu_delta = 0;
+
+    for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
+        const int base = b << 5;
+        const unsigned fullw = a.vis_full[b];
+        if (fullw == 0xffffffffu) {
+            if (lane == 0) a.nxt_nz[b] = 0u;
+            continue;
+        }
+        /* row_ptr tile of the block, one coalesced load per lane, handed out by shuffle */
+        const long long rp_lo = a.row_ptr[base + lane], rp_hi = a.row_ptr[base + lane + 1];
+        unsigned nzbits = 0u, fullbits = 0u;
+#pragma unroll 1
+        for (int it = 0; it < G; ++it) {
+            const int vi = it * VPI + grp;
+            const int u = base + vi;
+            const long long beg = __shfl_sync(0xffffffffu, rp_lo, vi);
+            const long long end = __shfl_sync(0xffffffffu, rp_hi, vi);
+            LW<NW> vis = lw_zero<NW>(), need = lw_zero<NW>();
+            bool cand = !((fullw >> vi) & 1u) && end > beg;
+            if (cand) {
+                vis = lw_load<NW>(a.visited, u);
+                need = lw_andn(live, vis);
+                cand = lw_any(need);
+            }
+            if (cand && sub == 0) ++examined;
+            LW<NW> acc = lw_zero<NW>();
+            bool go = cand;
+            long long e = beg + sub;
+            while (__any_sync(0xffffffffu, go)) {
+                acc = lw_or(acc, bu_gather<NW, U>(a, go, e, end, G, scanned, fetched));
+                e += (long long)G * U;
+                if (G >= 8) { /* early exit: every live lane this vertex misses has been found */
+                    const LW<NW> g = group_or<NW, G>(acc, gmask);
+                    if (lw_covers(g, need)) go = false;
+                }
+                if (e - sub >= end) go = false;
+            }
+            const LW<NW> found = lw_and(group_or<NW, G>(acc, gmask), need);
+            const bool has_new = cand && lw_any(found);
+            bool full_now = false;
+            if (has_new && sub == 0) {
+                const LW<NW> nv = lw_or(vis, found);
+                lw_store<NW>(a.visited, u, nv);
+                lw_store<NW>(a.nxt, u, found);
+                ++written;
+                if (lw_covers(nv, active)) { full_now = true; mu_delta -= end - beg; }
+            }
+            /* leaders' flags -> bits it*VPI .. it*VPI+VPI-1 of the block's bitmap words */
+            const bool f_new = __shfl_sync(0xffffffffu, (int)(has_new && sub == 0), (lane % VPI) * G) != 0;
+            const bool f_full = __shfl_sync(0xffffffffu, (int)full_now, (lane % VPI) * G) != 0;
+            nzbits |= __ballot_sync(0xffffffffu, f_new && lane < VPI) << (it * VPI);
+            fullbits |= __ballot_sync(0xffffffffu, f_full && lane < VPI) << (it * VPI);
+        }
+        if (lane == 0) {
+            a.nxt_nz[b] = nzbits;
+            if (fullbits) a.vis_full[b] = fullw | fullbits;
+        }
+    }
+    flush_counters(a.ctrl, scanned, fetched, examined, written);
+    mu_delta = (long long)warp_sum((ull)mu_delta);
+    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+}
+
+/* Hub rows: one warp per 1024-entry chunk.  Chunks of the same row share what they
+ * have found through hub_acc (atomic OR) and stop once the row's need is covered. */
+template <int NW, int U>
+__global__ void __launch_bounds__(CTA) bu_heavy_kernel(TravArgs a) {
+    const int lane = threadIdx.x & 31;
+    const LW<NW> live = lw_from<NW>(a.ctrl->live);
+    ull scanned = 0, fetched = 0, examined = 0, written = 0;
+    for (long long c = global_warp(); c < a.n_chunks; c += total_warps()) {
+        int k, u;
+        chunk_lookup(a, c, k, u);
+        if (test_bit(a.vis_full, u)) continue;
+        const LW<NW> need = lw_andn(live, lw_load<NW>(a.visited, u));
+        if (!lw_any(need)) continue;
+        LW<NW> known = lw_load_volatile<NW>(a.hub_acc, u);
+        if (lw_covers(known, need)) continue;
+        const long long beg = a.row_ptr[u] + (long long)k * MSBFS_CHUNK;
+        const long long end = min(beg + (long long)MSBFS_CHUNK, a.row_ptr[u + 1]);
+        if (lane == 0 && k == 0) ++examined;
+        for (long long e = beg + lane; e - lane < end; e += 32ll * U) {
+            const LW<NW> t = bu_gather<NW, U>(a, true, e, end, 32, scanned, fetched);
+            const LW<NW> fresh = lw_andn(lw_and(group_or<NW, 32>(t, 0xffffffffu), need), known);
+            if (lw_any(fresh)) {
+                if (lane == 0) {
+#pragma unroll
+                    for (int i = 0; i < NW; ++i)
+                        if (fresh.w[i]) atomicOr(&a.hub_acc[(long long)u * NW + i], fresh.w[i]);
+                    ++written;
+                }
+                __syncwarp();
+                known = lw_or(lw_load_volatile<NW>(a.hub_acc, u), fresh);
+            }
+            if (lw_covers(known, need)) break;
+        }
+    }
+    flush_counters(a.ctrl, scanned, fetched, examined, written);
+}
+
+template <int NW>
+__global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a) {
+    const int lane = threadIdx.x & 31;
+    const LW<NW> live = lw_from<NW>(a.ctrl->live);
+    const LW<NW> active = lw_from<NW>(a.ctrl->active);
+    long long mu_delta = 0;
+    for (int b = global_warp(); b < a.blk_heavy; b += total_warps()) {
+        const int u = (b << 5) + lane;
+        const unsigned fullw = a.vis_full[b];
+        bool has_new = false, full_now = false;
+        if (!((fullw >> lane) & 1u)) {
+            const LW<NW> x = lw_load<NW>(a.hub_acc, u);
+            if (lw_any(x)) {
+                lw_store<NW>(a.hub_acc, u, lw_zero<NW>());
+                const LW<NW> vis = lw_load<NW>(a.visited, u);
+                const LW<NW> found = lw_andn(lw_and(x, live), vis);
+                if (lw_any(found)) {
+                    const LW<NW> nv = lw_or(vis, found);
+                    lw_store<NW>(a.visited, u, nv);
+                    lw_store<NW>(a.nxt, u, found);
+                    has_new = true;
+                    if (lw_covers(nv, active)) { full_now = true; mu_delta -= a.row_ptr[u + 1] - a.row_ptr[u]; }
+                }
+            }
+        }
+        const unsigned nz = __ballot_sync(0xffffffffu, has_new);
+        const unsigned fb = __ballot_sync(0xffffffffu, full_now);
+        if (lane == 0) {
+            a.nxt_nz[b] = nz;
+            if (fb) a.vis_full[b] = fullw | fb;
+        }
+    }
+    mu_delta = (long long)warp_sum((ull)mu_delta);
+    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+}
+
+/* ------------------------------------------- per-lane counts (popcount) --- */
+
+/* 32 x 32 bit-matrix transpose across a warp: on return, bit i of lane j's word is
+ * bit j of lane i's input. */
+__device__ __forceinline__ unsigned warp_transpose32(unsigned x, int lane) {
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+        const int d = 16 >> s;
+        const unsigned m = (s == 0) ? 0x0000ffffu : (s == 1) ? 0x00ff00ffu : (s == 2) ? 0x0f0f0f0fu
+                         : (s == 3) ? 0x33333333u : 0x55555555u;
+        const unsigned p = __shfl_xor_sync(0xffffffffu, x, d);
+        x = (lane & d) ? ((x & ~m) | ((p >> d) & m)) : ((x & m) | ((p & m) << d));
+    }
+    return x;
+}
+
+/* Bit-sliced vertical counters: slice s holds bit s of a per-bit-position count.
+ * Adding a word is a ripple of (AND, XOR) pairs; 5 slices take 31 additions. */
+template <int NC> struct Csa {
+    static constexpr int K = 5;
+    unsigned sl[K][NC];
+    unsigned cnt[NC]; /* after flush(): this lane's bit position, chunk c */
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int s = 0; s < K; ++s)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) sl[s][c] = 0u;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) cnt[c] = 0u;
+    }
+    __device__ __forceinline__ void add(const ull* w) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            unsigned carry = (unsigned)(w[c >> 1] >> ((c & 1) * 32));
+#pragma unroll
+            for (int s = 0; s < K; ++s) {
+                const unsigned t = sl[s][c] & carry;
+                sl[s][c] ^= carry;
+                carry = t;
+            }
+        }
+    }
+    /* warp-collective */
+    __device__ __forceinline__ void flush(int lane) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+#pragma unroll
+            for (int s = 0; s < K; ++s) {
+                cnt[c] += (unsigned)__popc(warp_transpose32(sl[s][c], lane)) << s;
+                sl[s][c] = 0u;
+            }
+        }
+    }
+};
+
+/* mode 0: count the new frontier words (nxt, where nxt_nz) into ctrl->cnt, plus the
+ *         frontier's vertex and entry totals for the direction heuristic;
+ * mode 1: count visited words of vertices whose degree has bit `degbit` set into
+ *         out[] scaled by 2^degbit (reached CSR entries per lane, for TEPS). */
+template <int NW, int MODE>
+__global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int degbit, ull* __restrict__ out) {
+    constexpr int NC = 2 * NW;
+    __shared__ unsigned s_cnt[64 * NW];
+    for (int i = threadIdx.x; i < 64 * NW; i += CTA) s_cnt[i] = 0u;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    Csa<NC> csa;
+    csa.init();
+    int pending = 0;
+    ull nf = 0, mf = 0;
+    for (int b = global_warp(); b < nblk; b += total_warps()) {
+        const int v = (b << 5) + lane;
+        if (MODE == 0) {
+            const unsigned w = a.nxt_nz[b];
+            if (w == 0u) continue;
+            if ((w >> lane) & 1u) {
+                const LW<NW> x = lw_load<NW>(a.nxt, v);
+                csa.add(x.w);
+                ++nf;
+                mf += (ull)(a.row_ptr[v + 1] - a.row_ptr[v]);
+            }
+        } else {
+            const ull deg = (ull)(a.row_ptr[v + 1] - a.row_ptr[v]);
+            if ((deg >> degbit) & 1ull) {
+                const LW<NW> x = lw_load<NW>(a.visited, v);
+                csa.add(x.w);
+            }
+        }
+        if (++pending == 31) { csa.flush(lane); pending = 0; }
+    }
+    csa.flush(lane);
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+        if (csa.cnt[c]) atomicAdd(&s_cnt[c * 32 + lane], csa.cnt[c]);
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * NW; i += CTA) {
+        const unsigned v = s_cnt[i];
+        if (v) {
+            if (MODE == 0) atomicAdd(&a.ctrl->cnt[i], (ull)v);
+            else atomicAdd(&out[i], (ull)v << degbit);
+        }
+    }
+    if (MODE == 0) {
+        nf = warp_sum(nf);
+        mf = warp_sum(mf);
+        if (lane == 0 && nf) { atomicAdd(&a.ctrl->n_f, nf); atomicAdd(&a.ctrl->m_f, mf); }
+    }
+}
+
+/* ------------------------------------------------------ level bookkeeping --- */
+
+__global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz) {
+    const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
+    c->cnt[j] = 0ull;
+    c->sums[j] = 0ull;
+    if (j < MSBFS_MAX_NW) {
+        c->live[j] = 0ull;
+        ull m = 0ull;
+        const int lo = j * 64;
+        if (lanes >= lo + 64) m = ~0ull;
+        else if (lanes > lo) m = (1ull << (lanes - lo)) - 1ull;
+        c->active[j] = m;
+    }
+    if (j == 0) {
+        c->n_f = 0; c->m_f = 0; c->m_u = nnz;
+        c->scanned = c->words_fetched = c->examined = c->words_written = 0;
+        c->level = -1;
+    }
+}
+
+/* F(j) += (level + 1) * count(j)  (the reference's sum of distances, main.cu:81-87,
+ * taken level by level), live lanes, and the direction of the next level.
+ * `direction` is what the level just finished used (0 = injection). */
+__global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
+                                int direction, long long alpha, int force_direction) {
+    const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
+    const ull cnt = c->cnt[j];
+    c->sums[j] += (ull)(c->level + 1) * cnt;
+    c->cnt[j] = 0ull;
+    const unsigned bal = __ballot_sync(0xffffffffu, cnt != 0ull);
+    if ((j & 31) == 0) reinterpret_cast<unsigned*>(c->live)[j >> 5] = bal;
+    __syncthreads();
+    if (j == 0) {
+        const ull nf = c->n_f, mf = c->m_f;
+        const long long mu = c->m_u;
+        int next = (force_direction == 1 || force_direction == 2) ? force_direction
+                   : (((long long)mf * alpha < mu) ? 1 : 2);
+        if (c->log_pos < log_cap) {
+            LevelLog& l = log[c->log_pos];
+            l.level = c->level; l.direction = direction;
+            l.frontier_vertices = nf; l.frontier_entries = mf; l.unexplored_entries = mu;
+            l.scanned = c->scanned; l.words_fetched = c->words_fetched;
+            l.vertices_examined = c->examined; l.words_written = c->words_written;
+        }
+        c->log_pos += 1;
+        verdict->done = (nf == 0ull);
+        verdict->next_direction = next;
+        verdict->n_f = nf; verdict->m_f = mf; verdict->m_u = mu;
+        c->n_f = 0; c->m_f = 0;
+        c->scanned = c->words_fetched = c->examined = c->words_written = 0;
+        c->level += 1;
+        __threadfence_system();
+    }
+}
+
+__global__ void store_sums_kernel(const LevelCtrl* c, long long* __restrict__ sums, int group_base, int lanes) {
+    const int j = threadIdx.x;
+    if (j < lanes) sums[group_base + j] = (long long)c->sums[j];
+}
+
+/* ------------------------------------------------------------- host side --- */
+
+struct Launcher {
+    msbfs_handle* h;
+    TravArgs a;
+    long long launches = 0;
+    int grid_cap;
+
+    int grid_for_warps(long long warps) const {
+        long long blocks = (warps + (CTA / 32) - 1) / (CTA / 32);
+        return (int)std::max<long long>(1, std::min<long long>(blocks, grid_cap));
+    }
+};
+
+template <int NW>
+int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_out) {
+    cudaStream_t s = h->stream;
+    const int lanes_per_batch = 64 * NW;
+    const int K = h->q_groups;
+    const int nblk = h->n_pad / 32;
+    const size_t word_bytes = (size_t)h->n_pad * NW * sizeof(ull);
+
+    Launcher L;
+    L.h = h;
+    L.grid_cap = h->sm_count * 6;
+    TravArgs& a = L.a;
+    a.row_ptr = h->d_row_ptr; a.col = h->d_col;
+    a.visited = h->d_visited; a.cur = h->d_cur; a.nxt = h->d_nxt; a.acc = h->d_acc; a.hub_acc = h->d_hub_acc;
+    a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk; a.vis_full = h->d_bitmaps + 2 * (size_t)nblk;
+    a.ctrl = h->d_ctrl;
+    a.chunk_level_base = h->d_chunk_level_base; a.n_chunk_levels = h->n_chunk_levels; a.n_chunks = h->n_chunks;
+    a.n_pad = h->n_pad;
+    a.blk_heavy = h->blk_heavy; a.blk_warp = h->blk_warp; a.blk_g8 = h->blk_g8; a.blk_end = h->blk_end;
+
+    ull* d_reached = nullptr;
+    if (want_reached) {
+        MSBFS_CUDA(cudaMalloc(&d_reached, sizeof(ull) * MSBFS_MAX_LANES));
+        reached_out->assign((size_t)K, 0ull);
+    }
+
+    MSBFS_CUDA(cudaMemsetAsync(&h->d_ctrl->log_pos, 0, sizeof(int), s));
+    int batches = 0;
+    long long levels = 0, levels_td = 0, levels_bu = 0;
+
+    for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
+        const int lanes = std::min(lanes_per_batch, K - group_base);
+        init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz);
+        MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
+        MSBFS_CUDA(cudaMemsetAsync(h->d_bitmaps, 0, sizeof(unsigned) * 3 * (size_t)nblk, s));
+        a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk;
+        a.cur = h->d_cur; a.nxt = h->d_nxt;
+        inject_kernel<NW><<<L.grid_for_warps(lanes), CTA, 0, s>>>(a, h->d_perm, h->n, h->n_active, h->d_q_offsets,
+                                                                  h->d_q_sources, group_base, lanes);
+        td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk);
+        count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr);
+        epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, 0, h->opt_alpha,
+                                                       h->opt_direction);
+        L.launches += 5;
+        MSBFS_CUDA(cudaGetLastError());
+
+        for (;;) {
+            std::swap(a.cur, a.nxt);
+            std::swap(a.cur_nz, a.nxt_nz);
+            MSBFS_CUDA(cudaStreamSynchronize(s));
+            if (h->h_verdict->done) break;
+            const int dir = h->h_verdict->next_direction;
+            ++levels;
+            if (dir == 1) {
+                ++levels_td;
+                MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
+                if (a.n_chunks > 0) {
+                    td_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a);
+                    ++L.launches;
+                }
+                if (a.blk_warp > a.blk_heavy) {
+                    td_expand_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
+                    ++L.launches;
+                }
+                if (a.blk_g8 > a.blk_warp) {
+                    td_expand_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
+                    ++L.launches;
+                }
+                if (a.blk_end > a.blk_g8) {
+                    td_expand_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
+                    ++L.launches;
+                }
+                td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk);
+                ++L.launches;
+            } else {
+                ++levels_bu;
+                if (a.blk_heavy > 0) {
+                    if (a.n_chunks > 0) {
+                        bu_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a);
+                        ++L.launches;
+                    }
+                    bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_heavy), CTA, 0, s>>>(a);
+                    ++L.launches;
+                }
+                if (a.blk_warp > a.blk_heavy) {
+                    bu_sweep_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
+                    ++L.launches;
+                }
+                if (a.blk_g8 > a.blk_warp) {
+                    bu_sweep_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
+                    ++L.launches;
+                }
+                if (a.blk_end > a.blk_g8) {
+                    bu_sweep_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
+                    ++L.launches;
+                }
+            }
+            count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr);
+            epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, dir,
+                                                           h->opt_alpha, h->opt_direction);
+            L.launches += 2;
+            MSBFS_CUDA(cudaGetLastError());
+        }
+        store_sums_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_sums, group_base, lanes);
+        ++L.launches;
+
+        if (want_reached) {
+            MSBFS_CUDA(cudaMemsetAsync(d_reached, 0, sizeof(ull) * MSBFS_MAX_LANES, s));
+            for (int bit = 0; bit < 40; ++bit)
+                count_kernel<NW, 1><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, bit, d_reached);
+            ull tmp[MSBFS_MAX_LANES];
+            MSBFS_CUDA(cudaMemcpyAsync(tmp, d_reached, sizeof tmp, cudaMemcpyDeviceToHost, s));
+            MSBFS_CUDA(cudaStreamSynchronize(s));
+            for (int j = 0; j < lanes; ++j) (*reached_out)[(size_t)group_base + j] = tmp[j];
+        }
+    }
+    MSBFS_CUDA(cudaGetLastError());
+    if (d_reached) cudaFree(d_reached);
+
+    h->stats.lanes = lanes_per_batch;
+    h->stats.batches = batches;
+    h->stats.levels = levels;
+    h->stats.levels_top_down = levels_td;
+    h->stats.levels_bottom_up = levels_bu;
+    h->stats.kernel_launches = L.launches;
+    return MSBFS_OK;
+}
+
+int ensure_traversal_buffers(msbfs_handle* h, int nw) {
+    if (h->nw_alloc == nw && h->d_visited) return MSBFS_OK;
+    msbfs_release_traversal(h);
+    cudaStream_t s = h->stream;
+    const size_t word_bytes = (size_t)std::max(h->n_pad, 32) * nw * sizeof(ull);
+    const size_t nblk = (size_t)std::max(h->n_pad, 32) / 32;
+    MSBFS_CUDA(cudaMalloc(&h->d_visited, word_bytes));
+    MSBFS_CUDA(cudaMalloc(&h->d_cur, word_bytes));
+    MSBFS_CUDA(cudaMalloc(&h->d_nxt, word_bytes));
+    MSBFS_CUDA(cudaMalloc(&h->d_acc, word_bytes));
+    const size_t hub_bytes = (size_t)std::max(h->blk_heavy * 32, 32) * nw * sizeof(ull);
+    MSBFS_CUDA(cudaMalloc(&h->d_hub_acc, hub_bytes));
+    MSBFS_CUDA(cudaMalloc(&h->d_bitmaps, sizeof(unsigned) * 3 * nblk));
+    MSBFS_CUDA(cudaMalloc(&h->d_ctrl, sizeof(LevelCtrl)));
+    h->log_cap = 1 << 16;
+    MSBFS_CUDA(cudaMalloc(&h->d_log, sizeof(LevelLog) * (size_t)h->log_cap));
+    MSBFS_CUDA(cudaHostAlloc(&h->h_verdict, sizeof(LevelVerdict), cudaHostAllocMapped));
+    MSBFS_CUDA(cudaMemsetAsync(h->d_acc, 0, word_bytes, s));      /* invariant: zero between kernels */
+    MSBFS_CUDA(cudaMemsetAsync(h->d_hub_acc, 0, hub_bytes, s));   /* invariant: zero between kernels */
+    MSBFS_CUDA(cudaMemsetAsync(h->d_ctrl, 0, sizeof(LevelCtrl), s));
+    h->nw_alloc = nw;
+
+    /* Blackwell's 126 MB L2: keep the three bitmaps (n/8 bytes each — every random
+     * probe of the traversal hits them first) resident with an access-policy window. */
+    if (h->opt_l2_persist) {
+        int max_win = 0, max_persist = 0;
+        cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
+        const size_t want = sizeof(unsigned) * 3 * nblk;
+        if (max_win > 0 && max_persist > 0) {
+            const size_t win = std::min(want, (size_t)max_win);
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min((size_t)max_persist, win));
+            cudaStreamAttrValue attr;
+            std::memset(&attr, 0, sizeof attr);
+            attr.accessPolicyWindow.base_ptr = h->d_bitmaps;
+            attr.accessPolicyWindow.num_bytes = win;
+            attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)max_persist / (double)win);
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr);
+            cudaGetLastError(); /* best effort: a refusal only costs the hint */
+        }
+    }
+    return MSBFS_OK;
+}
+
+int pick_nw(const msbfs_handle* h) {
+    if (h->opt_lanes == 64) return 1;
+    if (h->opt_lanes == 128) return 2;
+    if (h->opt_lanes == 256) return 4;
+    if (h->q_groups <= 64) return 1;
+    if (h->q_groups <= 128) return 2;
+    return 4;
+}
+
+int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_out) {
+    if (!h->has_graph) return msbfs_fail(MSBFS_ERR_INVALID, "no graph loaded");
+    cudaStream_t s = h->stream;
+    const int K = h->q_groups;
+    h->stats.lanes = 0; h->stats.batches = 0; h->stats.levels = 0;
+    h->stats.levels_top_down = h->stats.levels_bottom_up = 0;
+    h->stats.scanned_top_down = h->stats.scanned_bottom_up = 0;
+    h->stats.frontier_vertices = h->stats.candidate_vertices = 0;
+    h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0;
+    h->level_log.clear();
+    if (K == 0) return MSBFS_OK;
+    if (h->n_active == 0) { /* no edges: every F is 0 */
+        MSBFS_CUDA(cudaMemsetAsync(h->d_sums, 0, sizeof(long long) * (size_t)K, s));
+        MSBFS_CUDA(cudaStreamSynchronize(s));
+        if (want_reached) reached_out->assign((size_t)K, 0ull);
+        return MSBFS_OK;
+    }
+    const int nw = pick_nw(h);
+    int rc = ensure_traversal_buffers(h, nw);
+    if (rc) return rc;
+
+    cudaEvent_t ev0, ev1;
+    MSBFS_CUDA(cudaEventCreate(&ev0));
+    MSBFS_CUDA(cudaEventCreate(&ev1));
+    MSBFS_CUDA(cudaEventRecord(ev0, s));
+    if (nw == 1) rc = run_batches<1>(h, want_reached, reached_out);
+    else if (nw == 2) rc = run_batches<2>(h, want_reached, reached_out);
+    else rc = run_batches<4>(h, want_reached, reached_out);
+    if (rc) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return rc; }
+    MSBFS_CUDA(cudaEventRecord(ev1, s));
+    MSBFS_CUDA(cudaEventSynchronize(ev1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    h->stats.run_ms = ms;
+
+    /* per-level log -> totals and algorithmic bytes (DESIGN.md "algorithmic bytes") */
+    int log_pos = 0;
+    MSBFS_CUDA(cudaMemcpy(&log_pos, &h->d_ctrl->log_pos, sizeof(int), cudaMemcpyDeviceToHost));
+    const int nlog = std::min(log_pos, h->log_cap);
+    h->level_log.resize((size_t)nlog);
+    if (nlog > 0)
+        MSBFS_CUDA(cudaMemcpy(h->level_log.data(), h->d_log, sizeof(LevelLog) * (size_t)nlog, cudaMemcpyDeviceToHost));
+    const long long w = 8ll * nw;
+    long long bytes = 0;
+    for (const LevelLog& l : h->level_log) {
+        h->stats.frontier_vertices += (int64_t)l.frontier_vertices;
+        if (l.direction == 1) h->stats.scanned_top_down += (int64_t)l.scanned;
+        if (l.direction == 2) { h->stats.scanned_bottom_up += (int64_t)l.scanned; h->stats.candidate_vertices += (int64_t)l.vertices_examined; }
+        /* col entry 4 B; every lane word moved (fetched through col, or stored) w B;
+         * every examined vertex: two row offsets 16 B + its own word w B;
+         * the new frontier is read once more by the count kernel: w B per vertex */
+        bytes += 4ll * (long long)l.scanned + w * (long long)l.words_fetched + (16ll + w) * (long long)l.vertices_examined
+               + 2ll * w * (long long)l.words_written + w * (long long)l.frontier_vertices;
+    }
+    /* per batch: clearing visited (w per vertex) and the bitmaps */
+    bytes += (long long)h->stats.batches * ((long long)h->n_pad * w + 3ll * (h->n_pad / 8));
+    h->stats.alg_bytes = bytes;
+    return MSBFS_OK;
+}
+
+} // namespace
+
+void msbfs_release_traversal(msbfs_handle* h) {
+    cudaFree(h->d_visited); h->d_visited = nullptr;
+    cudaFree(h->d_cur); h->d_cur = nullptr;
+    cudaFree(h->d_nxt); h->d_nxt = nullptr;
+    cudaFree(h->d_acc); h->d_acc = nullptr;
+    cudaFree(h->d_hub_acc); h->d_hub_acc = nullptr;
+    cudaFree(h->d_bitmaps); h->d_bitmaps = nullptr;
+    cudaFree(h->d_ctrl); h->d_ctrl = nullptr;
+    cudaFree(h->d_log); h->d_log = nullptr;
+    if (h->h_verdict) { cudaFreeHost(h->h_verdict); h->h_verdict = nullptr; }
+    h->nw_alloc = 0;
+}
+
+int msbfs_traverse(msbfs_handle* h) { return traverse_impl(h, false, nullptr); }
+
+int msbfs_reached_entries_impl(msbfs_handle* h, int64_t* out_entries, int32_t count) {
+    std::vector<ull> reached;
+    int rc = traverse_impl(h, true, &reached);
+    if (rc) return rc;
+    for (int32_t i = 0; i < count; ++i) out_entries[i] = (i < (int32_t)reached.size()) ? (int64_t)reached[(size_t)i] : 0;
+    return MSBFS_OK;
+}
