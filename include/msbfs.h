@@ -53,7 +53,8 @@ int msbfs_destroy(msbfs_t* h);
  *   "lanes"      0 = auto (64/128/256 by group count), or 64 / 128 / 256
  *   "direction"  0 = direction-optimizing, 1 = top-down only, 2 = bottom-up only
  *   "alpha"      top-down is chosen while frontier_entries * alpha < unexplored_entries
- *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off */
+ *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off
+ *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile) */
 int msbfs_set_option(msbfs_t* h, const char* key, int64_t value);
 
 /* ----------------------------------------------------------------- graph -- */
@@ -144,6 +145,25 @@ typedef struct msbfs_stats {
 } msbfs_stats;
 
 int msbfs_get_stats(msbfs_t* h, msbfs_stats* out);
+
+/* Per-kernel accounting of the last run, for roofline reporting.  With option
+ * "profile" = 1 every launch is bracketed by CUDA events on the handle's stream and
+ * `ms` is their sum; the counters are always kept.  alg_bytes = 4 B per scanned CSR
+ * entry + one lane word per word fetched + (16 B + one word) per vertex examined +
+ * two words per word written.  Slots: 0-3 top-down (chunked rows, 32, 8,
+ * 2 threads per vertex), 4-7 bottom-up (same bins), 8 top-down finalize, 9 bottom-up
+ * chunk finalize, 10 per-lane count, 11 bookkeeping.  Measurement only: nothing in
+ * the reference corresponds to it. */
+typedef struct msbfs_kernel_profile {
+    char    name[32];
+    int64_t launches;
+    double  ms;
+    int64_t alg_bytes;
+    int64_t scanned, words_fetched, vertices_examined, words_written;
+} msbfs_kernel_profile;
+
+int msbfs_num_kernel_slots(void);
+int msbfs_get_kernel_profile(msbfs_t* h, int slot, msbfs_kernel_profile* out);
 
 /* ----------------------------------------------- host-side file helpers -- */
 

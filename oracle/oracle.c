@@ -54,6 +54,46 @@ int oracle_build_csr(int32_t n, int64_t m, const int32_t* uv, int64_t** row_out,
     return 0;
 }
 
+/* Same adjacency multiset built by all host threads (atomic counting + atomic fill), for
+ * the multi-GiB bench inputs where the serial walk above takes minutes.  The order
+ * inside a row is then arbitrary; no hop distance or distance sum depends on it. */
+int oracle_build_csr_parallel(int32_t n, int64_t m, const int32_t* uv, int64_t** row_out, int32_t** col_out) {
+    if (n < 0 || m < 0) return -1;
+    int64_t* row = (int64_t*)calloc((size_t)n + 2, sizeof(int64_t));
+    int32_t* col = (int32_t*)malloc(sizeof(int32_t) * (size_t)(2 * m > 0 ? 2 * m : 1));
+    int64_t* cur = (int64_t*)malloc(sizeof(int64_t) * (size_t)(n > 0 ? n : 1));
+    if (!row || !col || !cur) { free(row); free(col); free(cur); return -2; }
+    int bad = 0;
+#pragma omp parallel for schedule(static) reduction(|:bad)
+    for (int64_t i = 0; i < m; ++i) {
+        int32_t u = uv[2 * i], v = uv[2 * i + 1];
+        if (u < 0 || u >= n || v < 0 || v >= n) { bad = 1; continue; }
+#pragma omp atomic
+        row[u + 1]++;
+#pragma omp atomic
+        row[v + 1]++;
+    }
+    if (bad) { free(row); free(col); free(cur); return -3; }
+    for (int32_t i = 0; i < n; ++i) row[i + 1] += row[i];
+#pragma omp parallel for schedule(static)
+    for (int32_t i = 0; i < n; ++i) cur[i] = row[i];
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < m; ++i) {
+        int32_t u = uv[2 * i], v = uv[2 * i + 1];
+        int64_t pu, pv;
+#pragma omp atomic capture
+        pu = cur[u]++;
+#pragma omp atomic capture
+        pv = cur[v]++;
+        col[pu] = v;
+        col[pv] = u;
+    }
+    free(cur);
+    *row_out = row;
+    *col_out = col;
+    return 0;
+}
+
 /* main.cu:92-117 — header int32 n, int64 m, then m x (int32 u, int32 v). */
 int oracle_load_graph_bin(const char* path, int32_t* n_out, int64_t* m_out, int32_t** uv_out) {
     FILE* f = fopen(path, "rb");

@@ -13,6 +13,8 @@ extern "C" {
 
 /* main.cu:106-129 */
 int oracle_build_csr(int32_t n, int64_t m, const int32_t* uv, int64_t** row_out, int32_t** col_out);
+/* same multiset, all host threads, row order arbitrary (large bench inputs only) */
+int oracle_build_csr_parallel(int32_t n, int64_t m, const int32_t* uv, int64_t** row_out, int32_t** col_out);
 /* main.cu:92-117 (returns the raw records; pair with oracle_build_csr) */
 int oracle_load_graph_bin(const char* path, int32_t* n_out, int64_t* m_out, int32_t** uv_out);
 /* main.cu:134-164 (+ extended container) */

@@ -50,6 +50,21 @@ class Stats(C.Structure):
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class KernelProfile(C.Structure):
+    """struct msbfs_kernel_profile (include/msbfs.h)."""
+
+    _fields_ = [
+        ("name", C.c_char * 32), ("launches", C.c_int64), ("ms", C.c_double), ("alg_bytes", C.c_int64),
+        ("scanned", C.c_int64), ("words_fetched", C.c_int64), ("vertices_examined", C.c_int64),
+        ("words_written", C.c_int64),
+    ]
+
+    def as_dict(self) -> dict:
+        d = {name: getattr(self, name) for name, _ in self._fields_}
+        d["name"] = self.name.decode()
+        return d
+
+
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 
@@ -73,6 +88,8 @@ SIGNATURES = {
     "msbfs_unpack_argmin": (C.c_int, [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_allreduce_min_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
     "msbfs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "msbfs_num_kernel_slots": (C.c_int, []),
+    "msbfs_get_kernel_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(KernelProfile)]),
     "msbfs_load_query_file": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "msbfs_write_query_file": (C.c_int, [C.c_char_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int]),
     "msbfs_write_graph_file": (C.c_int, [C.c_char_p, C.c_int32, C.c_int64, C.c_void_p]),
@@ -294,6 +311,14 @@ class Engine:
         st = Stats()
         _check(lib().msbfs_get_stats(self._h, C.byref(st)))
         return st.as_dict()
+
+    def kernel_profiles(self) -> list:
+        out = []
+        for slot in range(lib().msbfs_num_kernel_slots()):
+            kp = KernelProfile()
+            _check(lib().msbfs_get_kernel_profile(self._h, slot, C.byref(kp)))
+            out.append(kp.as_dict())
+        return out
 
     def solve(self, offsets: np.ndarray, sources: np.ndarray) -> Report:
         sums = self.run(offsets, sources)

@@ -124,6 +124,7 @@ extern "C" int msbfs_destroy(msbfs_t* h) {
     msbfs_release_graph(h);
     cudaFree(h->d_q_offsets); cudaFree(h->d_q_sources); cudaFree(h->d_sums); cudaFree(h->d_scalar);
     if (h->h_pinned_io) cudaFreeHost(h->h_pinned_io);
+    for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return MSBFS_OK;
@@ -143,6 +144,8 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
         h->opt_alpha = value;
     } else if (!std::strcmp(key, "l2_persist")) {
         h->opt_l2_persist = value != 0;
+    } else if (!std::strcmp(key, "profile")) {
+        h->opt_profile = value != 0;
     } else {
         return msbfs_fail(MSBFS_ERR_INVALID, "unknown option '%s'", key);
     }
@@ -311,6 +314,15 @@ extern "C" int msbfs_get_stats(msbfs_t* h, msbfs_stats* out) {
     h->stats.n = h->n; h->stats.n_active = h->n_active; h->stats.m = h->m; h->stats.csr_entries = h->nnz;
     h->stats.build_ms = h->build_ms;
     *out = h->stats;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_num_kernel_slots(void) { return MSBFS_NUM_SLOTS; }
+
+extern "C" int msbfs_get_kernel_profile(msbfs_t* h, int slot, msbfs_kernel_profile* out) {
+    if (!h || !out || slot < 0 || slot >= MSBFS_NUM_SLOTS)
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_kernel_profile: bad argument");
+    *out = h->slot_profile[slot];
     return MSBFS_OK;
 }
 

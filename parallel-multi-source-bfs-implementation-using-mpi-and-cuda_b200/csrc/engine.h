@@ -41,6 +41,14 @@ constexpr int MSBFS_DEG_HEAVY   = 1024;  /* deg >= this: row is split into chunk
 constexpr int MSBFS_DEG_WARP    = 64;    /* deg >  this: one warp per vertex           */
 constexpr int MSBFS_DEG_G8      = 8;     /* deg >  this: 8 threads per vertex, else 2  */
 
+/* kernels that are timed / accounted separately */
+enum KernelSlot {
+    SLOT_TD_HEAVY = 0, SLOT_TD_G32, SLOT_TD_G8, SLOT_TD_G2,
+    SLOT_BU_HEAVY, SLOT_BU_G32, SLOT_BU_G8, SLOT_BU_G2,
+    SLOT_TD_FINALIZE, SLOT_BU_HEAVY_FINALIZE, SLOT_COUNT, SLOT_OTHER,
+    MSBFS_NUM_SLOTS
+};
+
 /* per-level record kept on the device and copied back after a run */
 struct LevelLog {
     int32_t  level;        /* BFS depth that was expanded                */
@@ -64,6 +72,9 @@ struct LevelCtrl {
     unsigned long long scanned, words_fetched, examined, words_written; /* this level        */
     int level;                                 /* depth being expanded (-1 = injection)       */
     int log_pos;
+    /* per-kernel accumulators over a whole run (roofline accounting), see KernelSlot */
+    unsigned long long k_scanned[MSBFS_NUM_SLOTS], k_fetched[MSBFS_NUM_SLOTS], k_examined[MSBFS_NUM_SLOTS],
+        k_written[MSBFS_NUM_SLOTS];
 };
 
 /* what the host reads back after each level (pinned, written by the epilogue) */
@@ -141,6 +152,9 @@ struct msbfs_handle {
     /* stats of the last run */
     msbfs_stats stats{};
     std::vector<LevelLog> level_log;
+    int opt_profile = 0;                       /* time every kernel launch with CUDA events */
+    std::vector<cudaEvent_t> ev_pool;          /* start/stop pairs, grown on demand         */
+    msbfs_kernel_profile slot_profile[MSBFS_NUM_SLOTS]{};
 };
 
 /* graph_build.cu */

@@ -197,16 +197,16 @@ __device__ __forceinline__ void td_push(const TravArgs& a, const LW<NW>& f, long
     }
 }
 
-__device__ __forceinline__ void flush_counters(LevelCtrl* c, ull scanned, ull fetched, ull examined, ull written) {
+__device__ __forceinline__ void flush_counters(LevelCtrl* c, int slot, ull scanned, ull fetched, ull examined, ull written) {
     scanned = warp_sum(scanned);
     fetched = warp_sum(fetched);
     examined = warp_sum(examined);
     written = warp_sum(written);
     if ((threadIdx.x & 31) == 0) {
-        if (scanned) atomicAdd(&c->scanned, scanned);
-        if (fetched) atomicAdd(&c->words_fetched, fetched);
-        if (examined) atomicAdd(&c->examined, examined);
-        if (written) atomicAdd(&c->words_written, written);
+        if (scanned) { atomicAdd(&c->scanned, scanned); atomicAdd(&c->k_scanned[slot], scanned); }
+        if (fetched) { atomicAdd(&c->words_fetched, fetched); atomicAdd(&c->k_fetched[slot], fetched); }
+        if (examined) { atomicAdd(&c->examined, examined); atomicAdd(&c->k_examined[slot], examined); }
+        if (written) { atomicAdd(&c->words_written, written); atomicAdd(&c->k_written[slot], written); }
     }
 }
 
@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(CTA) td_expand_kernel(TravArgs a, int blk_lo, 
             td_push<NW, U>(a, f, beg + sub, end, G, scanned, fetched, written);
         }
     }
-    flush_counters(a.ctrl, scanned, fetched, examined, written);
+    flush_counters(a.ctrl, G == 32 ? SLOT_TD_G32 : G == 8 ? SLOT_TD_G8 : SLOT_TD_G2, scanned, fetched, examined, written);
 }
 
 /* chunk id -> (level k, vertex): level k holds vertices [0, base[k+1]-base[k]) */
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(CTA) td_heavy_kernel(TravArgs a) {
         if (lane == 0 && k == 0) ++examined;
         td_push<NW, U>(a, f, beg + lane, end, 32, scanned, fetched, written);
     }
-    flush_counters(a.ctrl, scanned, fetched, examined, written);
+    flush_counters(a.ctrl, SLOT_TD_HEAVY, scanned, fetched, examined, written);
 }
 
 /* acc -> new frontier.  acc already excludes visited lanes (td_push masks with
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, i
             if (fullbits) a.vis_full[b] = fullw | fullbits;
         }
     }
-    flush_counters(a.ctrl, scanned, fetched, examined, written);
+    flush_counters(a.ctrl, G == 32 ? SLOT_BU_G32 : G == 8 ? SLOT_BU_G8 : SLOT_BU_G2, scanned, fetched, examined, written);
     mu_delta = (long long)warp_sum((ull)mu_delta);
     if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
 }
@@ -434,7 +434,7 @@ __global__ void __launch_bounds__(CTA) bu_heavy_kernel(TravArgs a) {
             if (lw_covers(known, need)) break;
         }
     }
-    flush_counters(a.ctrl, scanned, fetched, examined, written);
+    flush_counters(a.ctrl, SLOT_BU_HEAVY, scanned, fetched, examined, written);
 }
 
 template <int NW>
@@ -645,11 +645,43 @@ __global__ void store_sums_kernel(const LevelCtrl* c, long long* __restrict__ su
 
 /* ------------------------------------------------------------- host side --- */
 
+constexpr size_t MAX_EVENT_PAIRS = 1u << 16;
+
 struct Launcher {
     msbfs_handle* h;
     TravArgs a;
     long long launches = 0;
     int grid_cap;
+    std::vector<int> pair_slot; /* slot of event pair i (events 2i, 2i+1 of h->ev_pool) */
+
+    /* bracket one launch with CUDA events on the launching stream (option "profile") */
+    template <class F> void timed(int slot, F&& launch) {
+        ++launches;
+        ++h->slot_profile[slot].launches;
+        const bool rec = h->opt_profile && pair_slot.size() < MAX_EVENT_PAIRS;
+        size_t i = pair_slot.size();
+        if (rec) {
+            while (h->ev_pool.size() < 2 * (i + 1)) {
+                cudaEvent_t e;
+                if (cudaEventCreate(&e) != cudaSuccess) { launch(); return; }
+                h->ev_pool.push_back(e);
+            }
+            cudaEventRecord(h->ev_pool[2 * i], h->stream);
+        }
+        launch();
+        if (rec) {
+            cudaEventRecord(h->ev_pool[2 * i + 1], h->stream);
+            pair_slot.push_back(slot);
+        }
+    }
+    void collect() {
+        for (size_t i = 0; i < pair_slot.size(); ++i) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, h->ev_pool[2 * i], h->ev_pool[2 * i + 1]) == cudaSuccess)
+                h->slot_profile[pair_slot[i]].ms += ms;
+        }
+        pair_slot.clear();
+    }
 
     int grid_for_warps(long long warps) const {
         long long blocks = (warps + (CTA / 32) - 1) / (CTA / 32);
@@ -683,24 +715,27 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
         reached_out->assign((size_t)K, 0ull);
     }
 
-    MSBFS_CUDA(cudaMemsetAsync(&h->d_ctrl->log_pos, 0, sizeof(int), s));
+    MSBFS_CUDA(cudaMemsetAsync(h->d_ctrl, 0, sizeof(LevelCtrl), s)); /* log_pos and the per-kernel accumulators */
     int batches = 0;
     long long levels = 0, levels_td = 0, levels_bu = 0;
 
     for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
         const int lanes = std::min(lanes_per_batch, K - group_base);
-        init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz);
+        L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz); });
         MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
         MSBFS_CUDA(cudaMemsetAsync(h->d_bitmaps, 0, sizeof(unsigned) * 3 * (size_t)nblk, s));
         a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk;
         a.cur = h->d_cur; a.nxt = h->d_nxt;
-        inject_kernel<NW><<<L.grid_for_warps(lanes), CTA, 0, s>>>(a, h->d_perm, h->n, h->n_active, h->d_q_offsets,
-                                                                  h->d_q_sources, group_base, lanes);
-        td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk);
-        count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr);
-        epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, 0, h->opt_alpha,
-                                                       h->opt_direction);
-        L.launches += 5;
+        L.timed(SLOT_OTHER, [&] {
+            inject_kernel<NW><<<L.grid_for_warps(lanes), CTA, 0, s>>>(a, h->d_perm, h->n, h->n_active, h->d_q_offsets,
+                                                                      h->d_q_sources, group_base, lanes);
+        });
+        L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
+        L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
+        L.timed(SLOT_OTHER, [&] {
+            epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, 0, h->opt_alpha,
+                                                           h->opt_direction);
+        });
         MSBFS_CUDA(cudaGetLastError());
 
         for (;;) {
@@ -713,55 +748,51 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             if (dir == 1) {
                 ++levels_td;
                 MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
-                if (a.n_chunks > 0) {
-                    td_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a);
-                    ++L.launches;
-                }
-                if (a.blk_warp > a.blk_heavy) {
-                    td_expand_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
-                    ++L.launches;
-                }
-                if (a.blk_g8 > a.blk_warp) {
-                    td_expand_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
-                    ++L.launches;
-                }
-                if (a.blk_end > a.blk_g8) {
-                    td_expand_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
-                    ++L.launches;
-                }
-                td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk);
-                ++L.launches;
+                if (a.n_chunks > 0)
+                    L.timed(SLOT_TD_HEAVY, [&] { td_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a); });
+                if (a.blk_warp > a.blk_heavy)
+                    L.timed(SLOT_TD_G32, [&] {
+                        td_expand_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
+                    });
+                if (a.blk_g8 > a.blk_warp)
+                    L.timed(SLOT_TD_G8, [&] {
+                        td_expand_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
+                    });
+                if (a.blk_end > a.blk_g8)
+                    L.timed(SLOT_TD_G2, [&] {
+                        td_expand_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
+                    });
+                L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
             } else {
                 ++levels_bu;
                 if (a.blk_heavy > 0) {
-                    if (a.n_chunks > 0) {
-                        bu_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a);
-                        ++L.launches;
-                    }
-                    bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_heavy), CTA, 0, s>>>(a);
-                    ++L.launches;
+                    if (a.n_chunks > 0)
+                        L.timed(SLOT_BU_HEAVY, [&] { bu_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a); });
+                    L.timed(SLOT_BU_HEAVY_FINALIZE, [&] {
+                        bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_heavy), CTA, 0, s>>>(a);
+                    });
                 }
-                if (a.blk_warp > a.blk_heavy) {
-                    bu_sweep_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
-                    ++L.launches;
-                }
-                if (a.blk_g8 > a.blk_warp) {
-                    bu_sweep_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
-                    ++L.launches;
-                }
-                if (a.blk_end > a.blk_g8) {
-                    bu_sweep_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
-                    ++L.launches;
-                }
+                if (a.blk_warp > a.blk_heavy)
+                    L.timed(SLOT_BU_G32, [&] {
+                        bu_sweep_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
+                    });
+                if (a.blk_g8 > a.blk_warp)
+                    L.timed(SLOT_BU_G8, [&] {
+                        bu_sweep_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
+                    });
+                if (a.blk_end > a.blk_g8)
+                    L.timed(SLOT_BU_G2, [&] {
+                        bu_sweep_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
+                    });
             }
-            count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr);
-            epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, dir,
-                                                           h->opt_alpha, h->opt_direction);
-            L.launches += 2;
+            L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
+            L.timed(SLOT_OTHER, [&] {
+                epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, dir,
+                                                               h->opt_alpha, h->opt_direction);
+            });
             MSBFS_CUDA(cudaGetLastError());
         }
-        store_sums_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_sums, group_base, lanes);
-        ++L.launches;
+        L.timed(SLOT_OTHER, [&] { store_sums_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_sums, group_base, lanes); });
 
         if (want_reached) {
             MSBFS_CUDA(cudaMemsetAsync(d_reached, 0, sizeof(ull) * MSBFS_MAX_LANES, s));
@@ -773,6 +804,8 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             for (int j = 0; j < lanes; ++j) (*reached_out)[(size_t)group_base + j] = tmp[j];
         }
     }
+    MSBFS_CUDA(cudaStreamSynchronize(s));
+    L.collect();
     MSBFS_CUDA(cudaGetLastError());
     if (d_reached) cudaFree(d_reached);
 
@@ -850,6 +883,13 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     h->stats.frontier_vertices = h->stats.candidate_vertices = 0;
     h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0;
     h->level_log.clear();
+    static const char* kSlotNames[MSBFS_NUM_SLOTS] = {"td_heavy", "td_expand_g32", "td_expand_g8", "td_expand_g2",
+                                                      "bu_heavy", "bu_sweep_g32", "bu_sweep_g8", "bu_sweep_g2",
+                                                      "td_finalize", "bu_heavy_finalize", "count", "bookkeeping"};
+    for (int i = 0; i < MSBFS_NUM_SLOTS; ++i) {
+        std::memset(&h->slot_profile[i], 0, sizeof h->slot_profile[i]);
+        std::strncpy(h->slot_profile[i].name, kSlotNames[i], sizeof h->slot_profile[i].name - 1);
+    }
     if (K == 0) return MSBFS_OK;
     if (h->n_active == 0) { /* no edges: every F is 0 */
         MSBFS_CUDA(cudaMemsetAsync(h->d_sums, 0, sizeof(long long) * (size_t)K, s));
@@ -885,6 +925,16 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     if (nlog > 0)
         MSBFS_CUDA(cudaMemcpy(h->level_log.data(), h->d_log, sizeof(LevelLog) * (size_t)nlog, cudaMemcpyDeviceToHost));
     const long long w = 8ll * nw;
+    {
+        LevelCtrl hc;
+        MSBFS_CUDA(cudaMemcpy(&hc, h->d_ctrl, sizeof hc, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < MSBFS_NUM_SLOTS; ++i) {
+            msbfs_kernel_profile& p = h->slot_profile[i];
+            p.scanned = (int64_t)hc.k_scanned[i]; p.words_fetched = (int64_t)hc.k_fetched[i];
+            p.vertices_examined = (int64_t)hc.k_examined[i]; p.words_written = (int64_t)hc.k_written[i];
+            p.alg_bytes = 4ll * p.scanned + w * p.words_fetched + (16ll + w) * p.vertices_examined + 2ll * w * p.words_written;
+        }
+    }
     long long bytes = 0;
     for (const LevelLog& l : h->level_log) {
         h->stats.frontier_vertices += (int64_t)l.frontier_vertices;

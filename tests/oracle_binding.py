@@ -27,6 +27,8 @@ def lib() -> C.CDLL:
         h = C.CDLL(LIB)
         h.oracle_build_csr.restype = C.c_int
         h.oracle_build_csr.argtypes = [C.c_int32, C.c_int64, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        h.oracle_build_csr_parallel.restype = C.c_int
+        h.oracle_build_csr_parallel.argtypes = h.oracle_build_csr.argtypes
         h.oracle_load_graph_bin.restype = C.c_int
         h.oracle_load_graph_bin.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]
         h.oracle_load_query_bin.restype = C.c_int
@@ -51,11 +53,12 @@ def _p(a: np.ndarray) -> C.c_void_p:
 class Csr:
     """CSR built by the oracle (record order per row, both directions; main.cu:106-129)."""
 
-    def __init__(self, n: int, uv: np.ndarray):
+    def __init__(self, n: int, uv: np.ndarray, parallel: bool = False):
         uv = np.ascontiguousarray(uv, dtype=np.int32).reshape(-1, 2)
         self.n, self.m = int(n), int(uv.shape[0])
         row, col = C.c_void_p(), C.c_void_p()
-        rc = lib().oracle_build_csr(self.n, self.m, _p(uv) if uv.size else None, C.byref(row), C.byref(col))
+        build = lib().oracle_build_csr_parallel if parallel else lib().oracle_build_csr
+        rc = build(self.n, self.m, _p(uv) if uv.size else None, C.byref(row), C.byref(col))
         if rc != 0:
             raise ValueError(f"oracle_build_csr failed with {rc}")
         self._row, self._col = row, col

@@ -1,0 +1,150 @@
+"""CPU-side checks of the C-ABI library: it loads without a GPU, exports every symbol
+include/msbfs.h declares, its host-only entry points behave like the reference's host
+code, and the compute entry points fail loudly (no fallback) when there is no device."""
+import os
+import re
+import struct
+
+import numpy as np
+import pytest
+
+
+def declared_symbols(header_path):
+    text = open(header_path).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(msbfs_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    names = declared_symbols(pkg.HEADER_PATH)
+    assert len(names) >= 25
+    lib = pkg.lib()
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/msbfs.h but not exported"
+    assert set(names) == set(pkg.SIGNATURES), "python binding table and header disagree"
+
+
+def test_library_has_sm100a_code(pkg):
+    import subprocess
+    out = subprocess.run(["/usr/local/cuda/bin/cuobjdump", "--list-elf", pkg.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump not available")
+    assert "sm_100a" in out.stdout
+
+
+def test_no_gpu_fails_loudly(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.MsbfsError) as e:
+        pkg.Engine(0)
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_argmin_matches_reference_rule(pkg, ob):
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        k = int(rng.integers(0, 12))
+        sums = rng.integers(0, 5, size=k).astype(np.int64)
+        assert pkg.argmin(sums) == ob.argmin(sums)
+    assert pkg.argmin(np.zeros(0, np.int64)) == (-1, -1)
+
+
+def test_packed_argmin(pkg):
+    sums = np.array([10, 10, 7, 7], dtype=np.int64)
+    assert pkg.unpack_argmin(pkg.argmin_packed(sums, 0)) == (2, 7)
+    assert pkg.unpack_argmin(pkg.argmin_packed(sums, 1000)) == (1002, 7)
+    assert pkg.argmin_packed(np.zeros(0, np.int64), 5) == (1 << 64) - 1
+    assert pkg.unpack_argmin((1 << 64) - 1) == (-1, -1)
+    # ties across shards: the smaller global id must win under a plain unsigned min
+    a = pkg.argmin_packed(np.array([5, 3], dtype=np.int64), 0)
+    b = pkg.argmin_packed(np.array([3, 9], dtype=np.int64), 2)
+    assert pkg.unpack_argmin(min(a, b)) == (1, 3)
+    with pytest.raises(pkg.MsbfsError):
+        pkg.argmin_packed(np.array([1 << 40], dtype=np.int64), 0)
+    with pytest.raises(pkg.MsbfsError):
+        pkg.argmin_packed(np.array([1], dtype=np.int64), (1 << 24) - 1 + 1)
+
+
+def test_query_file_reference_format_bytes(pkg, ob, tmp_path, golden_dir):
+    """The writer emits the reference layout byte for byte (main.cu:143-161) and the
+    reader agrees with the oracle's reader on the committed files."""
+    offs = np.array([0, 1, 1, 3, 4], dtype=np.int64)
+    src = np.array([2, 100, -3, 0], dtype=np.int32)
+    p = str(tmp_path / "q.bin")
+    pkg.write_query_file(p, offs, src)
+    assert open(p, "rb").read() == open(os.path.join(golden_dir, "kat2.query.bin"), "rb").read()
+    for name in os.listdir(golden_dir):
+        if name.endswith(".query.bin"):
+            a = pkg.load_query_file(os.path.join(golden_dir, name))
+            b = ob.load_query_file(os.path.join(golden_dir, name))
+            assert a[0].tolist() == b[0].tolist() and a[1].tolist() == b[1].tolist()
+    # K = 0 is the single byte 0x00
+    pkg.write_query_file(p, np.array([0], dtype=np.int64), np.zeros(0, np.int32))
+    assert open(p, "rb").read() == b"\x00"
+    o, s = pkg.load_query_file(p)
+    assert o.tolist() == [0] and s.size == 0
+
+
+def test_query_file_extended_format(pkg, ob, tmp_path):
+    rng = np.random.default_rng(0)
+    sizes = rng.integers(0, 400, size=700)
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    src = rng.integers(-10, 1 << 20, size=int(offs[-1])).astype(np.int32)
+    p = str(tmp_path / "ext.bin")
+    pkg.write_query_file(p, offs, src)
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"\x00MSBFSQ2" and struct.unpack("<I", raw[8:12])[0] == 700
+    o, s = pkg.load_query_file(p)
+    assert o.tolist() == offs.tolist() and s.tolist() == src.tolist()
+    o2, s2 = ob.load_query_file(p)
+    assert o2.tolist() == offs.tolist() and s2.tolist() == src.tolist()
+    with pytest.raises(pkg.MsbfsError):
+        pkg.load_query_file(str(tmp_path / "missing.bin"))
+    open(p, "wb").write(raw[:-3])
+    with pytest.raises(pkg.MsbfsError):
+        pkg.load_query_file(p)
+
+
+def test_graph_file_writer_layout(pkg, ob, tmp_path, golden_dir):
+    uv = np.array([(0, 1), (1, 2), (2, 3), (3, 4), (2, 2), (0, 1)], dtype=np.int32)
+    p = str(tmp_path / "g.bin")
+    pkg.write_graph_file(p, 7, uv)
+    assert open(p, "rb").read() == open(os.path.join(golden_dir, "kat_g7.graph.bin"), "rb").read()
+    n, back = ob.load_graph_file(p)
+    assert n == 7 and back.tolist() == uv.tolist()
+
+
+def test_generators_are_deterministic_and_in_range(pkg):
+    for kind, p0, p1, m in [(pkg.GEN_RMAT, 10, 0, 5000), (pkg.GEN_KRON, 10, 0, 5000),
+                            (pkg.GEN_LATTICE, 9, 7, pkg.lattice_num_edges(9, 7)), (pkg.GEN_ER, 1000, 0, 5000)]:
+        n = pkg.gen_num_vertices(kind, p0, p1)
+        a = pkg.gen_edges_host(kind, p0, p1, m, 42)
+        b = pkg.gen_edges_host(kind, p0, p1, m, 42)
+        assert np.array_equal(a, b) and a.min() >= 0 and a.max() < n
+        if kind != pkg.GEN_LATTICE:
+            assert not np.array_equal(a, pkg.gen_edges_host(kind, p0, p1, m, 43))
+    # lattice: every vertex has 2..4 neighbours, no duplicates
+    uv = pkg.gen_edges_host(pkg.GEN_LATTICE, 9, 7, pkg.lattice_num_edges(9, 7), 0)
+    deg = np.bincount(uv.ravel(), minlength=63)
+    assert deg.min() == 2 and deg.max() == 4 and len({tuple(e) for e in uv.tolist()}) == len(uv)
+    # kron is rmat under a bijection of the labels
+    r = pkg.gen_edges_host(pkg.GEN_RMAT, 10, 0, 5000, 42)
+    k = pkg.gen_edges_host(pkg.GEN_KRON, 10, 0, 5000, 42)
+    mapping = {}
+    for a_, b_ in zip(r.ravel().tolist(), k.ravel().tolist()):
+        assert mapping.setdefault(a_, b_) == b_
+    assert len(set(mapping.values())) == len(mapping)
+    offs, src = pkg.gen_queries_host(1000, 7, 5, 1)
+    assert offs.tolist() == [0, 5, 10, 15, 20, 25, 30, 35] and src.min() >= 0 and src.max() < 1000
+
+
+def test_shard_ranges_cover_everything(pkg):
+    for k in [0, 1, 255, 256, 257, 1024, 4096, 5000]:
+        for world in [1, 2, 3, 4, 8]:
+            covered = []
+            for r in range(world):
+                a, b = pkg.shard_range(k, r, world)
+                assert 0 <= a <= b <= k
+                covered += list(range(a, b))
+            assert covered == list(range(k))
