@@ -276,6 +276,9 @@ def run_ours(args, wl, rank, local_rank, world):
     eng.set_option("profile", 1)
     if args.alpha:
         eng.set_option("alpha", args.alpha)
+    for kv in args.opt:
+        key, val = kv.split("=")
+        eng.set_option(key, int(val))
     if args.lanes:
         eng.set_option("lanes", args.lanes)
     t0 = time.time()
@@ -382,6 +385,11 @@ def run_ours(args, wl, rank, local_rank, world):
     e2e_s = reduce_max(sum(e2e_t)) / args.steps
     assert best_e == best
 
+    if rank == 0 and args.level_log:
+        with open(args.level_log, "w") as f:
+            for rec in eng.level_log():
+                f.write(json.dumps(rec) + "\n")
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -473,6 +481,8 @@ def main():
     ap.add_argument("--ref-groups", type=int, default=32, help="groups fed to the reference host build per step")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--force-port", action="store_true", help="reference arm: always use the oracle port")
+    ap.add_argument("--level-log", default="", help="write the per-level counters of the last step (JSON lines)")
+    ap.add_argument("--opt", action="append", default=[], help="engine option key=value (experiments)")
     ap.add_argument("--alpha", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=0)
     args = ap.parse_args()

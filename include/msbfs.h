@@ -162,6 +162,24 @@ typedef struct msbfs_kernel_profile {
     int64_t scanned, words_fetched, vertices_examined, words_written;
 } msbfs_kernel_profile;
 
+/* One record per BFS level of the last run (all batches, in execution order); the
+ * counters behind MSBFS_STATS and the roofline accounting.  direction: 0 = source
+ * injection, 1 = top-down, 2 = bottom-up.  Returns the number of records through
+ * count_out (at most `capacity` are copied). */
+typedef struct msbfs_level_record {
+    int32_t  level;
+    int32_t  direction;
+    uint64_t frontier_vertices;   /* vertices that got a non-empty new frontier word */
+    uint64_t frontier_entries;    /* their CSR entries                               */
+    int64_t  unexplored_entries;  /* CSR entries of vertices some lane still misses  */
+    uint64_t scanned;             /* CSR entries scanned                             */
+    uint64_t words_fetched;       /* lane words fetched through col                  */
+    uint64_t vertices_examined;
+    uint64_t words_written;
+} msbfs_level_record;
+
+int msbfs_get_level_log(msbfs_t* h, msbfs_level_record* out, int32_t capacity, int32_t* count_out);
+
 int msbfs_num_kernel_slots(void);
 int msbfs_get_kernel_profile(msbfs_t* h, int slot, msbfs_kernel_profile* out);
 

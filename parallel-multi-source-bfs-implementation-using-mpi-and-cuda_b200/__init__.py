@@ -65,6 +65,16 @@ class KernelProfile(C.Structure):
         return d
 
 
+class LevelRecord(C.Structure):
+    """struct msbfs_level_record (include/msbfs.h)."""
+
+    _fields_ = [
+        ("level", C.c_int32), ("direction", C.c_int32), ("frontier_vertices", C.c_uint64),
+        ("frontier_entries", C.c_uint64), ("unexplored_entries", C.c_int64), ("scanned", C.c_uint64),
+        ("words_fetched", C.c_uint64), ("vertices_examined", C.c_uint64), ("words_written", C.c_uint64),
+    ]
+
+
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 
@@ -88,6 +98,7 @@ SIGNATURES = {
     "msbfs_unpack_argmin": (C.c_int, [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_allreduce_min_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
     "msbfs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "msbfs_get_level_log": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
     "msbfs_num_kernel_slots": (C.c_int, []),
     "msbfs_get_kernel_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(KernelProfile)]),
     "msbfs_load_query_file": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
@@ -311,6 +322,12 @@ class Engine:
         st = Stats()
         _check(lib().msbfs_get_stats(self._h, C.byref(st)))
         return st.as_dict()
+
+    def level_log(self, capacity: int = 1 << 16) -> list:
+        buf = (LevelRecord * capacity)()
+        cnt = C.c_int32()
+        _check(lib().msbfs_get_level_log(self._h, buf, capacity, C.byref(cnt)))
+        return [{name: getattr(buf[i], name) for name, _ in LevelRecord._fields_} for i in range(min(cnt.value, capacity))]
 
     def kernel_profiles(self) -> list:
         out = []

@@ -144,6 +144,20 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
         h->opt_alpha = value;
     } else if (!std::strcmp(key, "l2_persist")) {
         h->opt_l2_persist = value != 0;
+    } else if (!std::strcmp(key, "deg_thread")) {
+        if (value < 0 || value > 1024) return msbfs_fail(MSBFS_ERR_INVALID, "deg_thread out of range");
+        h->opt_deg_thread = (int)value;
+    } else if (!std::strcmp(key, "deg_warp")) {
+        if (value < 0 || value > 65536) return msbfs_fail(MSBFS_ERR_INVALID, "deg_warp out of range");
+        h->opt_deg_warp = (int)value;
+    } else if (!std::strcmp(key, "deg_heavy")) {
+        if (value < MSBFS_CHUNK || value > (1 << 30)) return msbfs_fail(MSBFS_ERR_INVALID, "deg_heavy out of range");
+        h->opt_deg_heavy = (int)value;
+    } else if (!std::strcmp(key, "seg")) {
+        if (value < 8 || value > (1 << 20)) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
+        h->opt_seg = (int)value;
+    } else if (!std::strcmp(key, "mid_variant")) {
+        h->opt_mid_variant = (int)value;
     } else if (!std::strcmp(key, "profile")) {
         h->opt_profile = value != 0;
     } else {
@@ -314,6 +328,17 @@ extern "C" int msbfs_get_stats(msbfs_t* h, msbfs_stats* out) {
     h->stats.n = h->n; h->stats.n_active = h->n_active; h->stats.m = h->m; h->stats.csr_entries = h->nnz;
     h->stats.build_ms = h->build_ms;
     *out = h->stats;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_get_level_log(msbfs_t* h, msbfs_level_record* out, int32_t capacity, int32_t* count_out) {
+    if (!h || !count_out || capacity < 0 || (capacity > 0 && !out))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_level_log: bad argument");
+    static_assert(sizeof(msbfs_level_record) == sizeof(LevelLog), "level record layouts must match");
+    const int32_t total = (int32_t)h->level_log.size();
+    const int32_t ncopy = total < capacity ? total : capacity;
+    if (ncopy > 0) std::memcpy(out, h->level_log.data(), sizeof(LevelLog) * (size_t)ncopy);
+    *count_out = total;
     return MSBFS_OK;
 }
 

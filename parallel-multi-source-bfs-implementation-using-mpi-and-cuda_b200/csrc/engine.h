@@ -72,6 +72,7 @@ struct LevelCtrl {
     unsigned long long scanned, words_fetched, examined, words_written; /* this level        */
     int level;                                 /* depth being expanded (-1 = injection)       */
     int log_pos;
+    unsigned heavy_frontier;                   /* new frontier touches a chunked (hub) row    */
     /* per-kernel accumulators over a whole run (roofline accounting), see KernelSlot */
     unsigned long long k_scanned[MSBFS_NUM_SLOTS], k_fetched[MSBFS_NUM_SLOTS], k_examined[MSBFS_NUM_SLOTS],
         k_written[MSBFS_NUM_SLOTS];
@@ -81,6 +82,8 @@ struct LevelCtrl {
 struct LevelVerdict {
     int32_t done;
     int32_t next_direction;
+    int32_t heavy_frontier;
+    int32_t pad_;
     uint64_t n_f, m_f;
     int64_t m_u;
 };
@@ -105,6 +108,14 @@ struct TravArgs {
     int blk_warp;   /*                 [blk_heavy, blk_warp)  : warp per vertex */
     int blk_g8;     /*                 [blk_warp, blk_g8)     : 8 threads/vertex */
     int blk_end;    /*                 [blk_g8, blk_end)      : 2 threads/vertex */
+    /* bottom-up: rows longer than `seg` entries are cut into segments of `seg`; segment
+     * k of vertex u is work item seg_level_base[k] + u (level-major: the first segments
+     * of all long rows come first).  Blocks [0, blk_multi) hold the long rows. */
+    const long long* seg_level_base; /* [n_seg_levels + 1] */
+    int n_seg_levels;
+    long long n_seg_items;
+    int seg;
+    int blk_multi;
 };
 
 struct msbfs_handle {
@@ -122,6 +133,9 @@ struct msbfs_handle {
     long long* d_chunk_level_base = nullptr;
     int n_chunk_levels = 0;
     long long n_chunks = 0;
+    long long* d_seg_level_base = nullptr;
+    int n_seg_levels = 0, blk_multi = 0, seg = 256;
+    long long n_seg_items = 0;
     bool has_graph = false;
     double build_ms = 0.0;
 
@@ -147,6 +161,9 @@ struct msbfs_handle {
 
     /* options */
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
+    int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
+    int opt_mid_variant = 0;                   /* experiment knob: kernel shape of the middle bin */
+    int opt_seg = 256;                         /* bottom-up segment length (next graph load)      */
     long long opt_alpha = 8;
 
     /* stats of the last run */

@@ -94,6 +94,21 @@ __global__ void bin_bounds_kernel(const unsigned int* __restrict__ deg_sorted, i
     out[t] = lo;
 }
 
+/* cnt[k] = number of vertices (of the first n_multi, degrees descending) with more than
+ * k * seg entries, for k in [0, levels]; cnt[levels] = 0 */
+__global__ void seg_level_count_kernel(const unsigned int* __restrict__ deg_sorted, int n_multi, int seg, int levels,
+                                       long long* __restrict__ cnt) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > levels) return;
+    const unsigned long long limit = (unsigned long long)k * (unsigned long long)seg;
+    int lo = 0, hi = n_multi;
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+        if ((unsigned long long)deg_sorted[mid] > limit) lo = mid + 1; else hi = mid;
+    }
+    cnt[k] = (k == levels) ? 0 : lo;
+}
+
 struct DevBuf {
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -114,6 +129,7 @@ void msbfs_release_graph(msbfs_handle* h) {
     cudaFree(h->d_row_ptr); h->d_row_ptr = nullptr;
     cudaFree(h->d_col); h->d_col = nullptr;
     cudaFree(h->d_chunk_level_base); h->d_chunk_level_base = nullptr;
+    cudaFree(h->d_seg_level_base); h->d_seg_level_base = nullptr;
     h->has_graph = false;
     h->n = h->n_active = h->n_pad = 0;
     h->m = h->nnz = 0;
@@ -195,7 +211,7 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
     /* degree bins over the sorted order (block = 32 consecutive internal ids) */
     {
         DevBuf lim, out;
-        const unsigned limits[3] = {MSBFS_DEG_HEAVY - 1, MSBFS_DEG_WARP, MSBFS_DEG_G8};
+        const unsigned limits[3] = {(unsigned)h->opt_deg_heavy - 1u, (unsigned)h->opt_deg_warp, (unsigned)h->opt_deg_thread};
         int bounds[3] = {0, 0, 0};
         MSBFS_CUDA(lim.alloc(sizeof limits));
         MSBFS_CUDA(out.alloc(sizeof bounds));
@@ -238,6 +254,42 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
         MSBFS_CUDA(cudaMemcpyAsync(h->d_chunk_level_base, base.data(), sizeof(long long) * base.size(),
                                    cudaMemcpyHostToDevice, s));
         MSBFS_CUDA(cudaStreamSynchronize(s));
+    }
+
+    /* bottom-up segments of the long rows (deg > seg), level-major */
+    {
+        const int seg = h->opt_seg;
+        DevBuf lim, out;
+        const unsigned limit = (unsigned)seg;
+        int first_short = 0;
+        unsigned maxdeg = 0;
+        MSBFS_CUDA(lim.alloc(sizeof limit));
+        MSBFS_CUDA(out.alloc(sizeof first_short));
+        MSBFS_CUDA(cudaMemcpyAsync(lim.p, &limit, sizeof limit, cudaMemcpyHostToDevice, s));
+        bin_bounds_kernel<<<1, 32, 0, s>>>(deg_sorted.as<unsigned>(), n_active, lim.as<unsigned>(), 1, out.as<int>());
+        MSBFS_CUDA(cudaGetLastError());
+        MSBFS_CUDA(cudaMemcpyAsync(&first_short, out.p, sizeof first_short, cudaMemcpyDeviceToHost, s));
+        if (n_active > 0) MSBFS_CUDA(cudaMemcpyAsync(&maxdeg, deg_sorted.p, sizeof maxdeg, cudaMemcpyDeviceToHost, s));
+        MSBFS_CUDA(cudaStreamSynchronize(s));
+        const int nblk = n_pad / 32;
+        h->seg = seg;
+        h->blk_multi = std::min(nblk, (first_short + 31) / 32);
+        const int n_multi = std::min(h->blk_multi * 32, n_active);
+        const int levels = n_multi > 0 ? (int)(((long long)maxdeg + seg - 1) / seg) : 0;
+        h->n_seg_levels = levels;
+        MSBFS_CUDA(cudaMalloc(&h->d_seg_level_base, sizeof(long long) * (size_t)(levels + 2)));
+        DevBuf cnt, tmp4;
+        MSBFS_CUDA(cnt.alloc(sizeof(long long) * (size_t)(levels + 2)));
+        seg_level_count_kernel<<<(levels + 1 + T - 1) / T, T, 0, s>>>(deg_sorted.as<unsigned>(), n_multi, seg, levels, cnt.as<long long>());
+        MSBFS_CUDA(cudaGetLastError());
+        size_t tb = 0;
+        MSBFS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.as<long long>(), h->d_seg_level_base, levels + 1, s));
+        MSBFS_CUDA(tmp4.alloc(tb));
+        MSBFS_CUDA(cub::DeviceScan::ExclusiveSum(tmp4.p, tb, cnt.as<long long>(), h->d_seg_level_base, levels + 1, s));
+        long long total = 0;
+        MSBFS_CUDA(cudaMemcpyAsync(&total, h->d_seg_level_base + levels, sizeof total, cudaMemcpyDeviceToHost, s));
+        MSBFS_CUDA(cudaStreamSynchronize(s));
+        h->n_seg_items = total;
     }
 
     /* the degree scratch is no longer needed: release before the big key buffers */

@@ -197,7 +197,7 @@ __device__ __forceinline__ void td_push(const TravArgs& a, const LW<NW>& f, long
     }
 }
 
-__device__ __forceinline__ void flush_counters(LevelCtrl* c, int slot, ull scanned, ull fetched, ull examined, ull written) {
+__device__ __forceinline__ void flush_counters(LevelCtrl* c, int slot, ull scanned, ull fetched, ull examined, ull written) { /* per-thread counts may be 32-bit: a thread never scans 2^32 entries in one launch */
     scanned = warp_sum(scanned);
     fetched = warp_sum(fetched);
     examined = warp_sum(examined);
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
  * entries are each issued back to back.  Returns the OR of the fetched words. */
 template <int NW, int U>
 __device__ __forceinline__ LW<NW> bu_gather(const TravArgs& a, bool go, long long e, long long end, int stride,
-                                            ull& scanned, ull& fetched) {
+                                            unsigned& scanned, unsigned& fetched) {
     int v[U];
     bool ok[U];
 #pragma unroll
@@ -312,30 +312,80 @@ __device__ __forceinline__ LW<NW> bu_gather(const TravArgs& a, bool go, long lon
         scanned += ok[k];
         ok[k] = ok[k] && test_bit(a.cur_nz, v[k]);
     }
-    LW<NW> x[U];
+    LW<NW> t = lw_zero<NW>();
 #pragma unroll
     for (int k = 0; k < U; ++k) {
-        x[k] = ok[k] ? lw_load<NW>(a.cur, v[k]) : lw_zero<NW>();
+        if (ok[k]) t = lw_or(t, lw_load<NW>(a.cur, v[k]));
         fetched += ok[k];
     }
-    LW<NW> t = x[0];
-#pragma unroll
-    for (int k = 1; k < U; ++k) t = lw_or(t, x[k]);
     return t;
 }
 
-/* A warp owns 32 consecutive vertices and handles 32/G of them at a time, G threads
- * per vertex.  Degrees are sorted, so the vertices of a warp have similar row
- * lengths and the warp-uniform inner loop wastes little. */
+/* The block's result bits: nxt_nz is fully rewritten every bottom-up level. */
+__device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, int lane, unsigned fullw, unsigned nzbits,
+                                                    unsigned fullbits) {
+    if (lane == 0) {
+        a.nxt_nz[b] = nzbits;
+        if (fullbits) a.vis_full[b] = fullw | fullbits;
+    }
+}
+
+/* Rows of at most MSBFS_DEG_G8 entries: one thread per vertex, no cross-thread
+ * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
+ * each thread leaves its loop as soon as its own need is covered. */
+template <int NW, int U>
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
+    const int lane = threadIdx.x & 31;
+    unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
+    long long mu_delta = 0;
+    for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
+        const unsigned fullw = a.vis_full[b];
+        if (fullw == 0xffffffffu) {
+            if (lane == 0) a.nxt_nz[b] = 0u;
+            continue;
+        }
+        const int u = (b << 5) + lane;
+        const long long beg = a.row_ptr[u], end = a.row_ptr[u + 1];
+        bool has_new = false, full_now = false;
+        if (!((fullw >> lane) & 1u) && end > beg) {
+            const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
+            if (lw_any(need)) {
+                ++examined;
+                LW<NW> acc = lw_zero<NW>();
+                for (long long e = beg; e < end; e += U) {
+                    acc = lw_or(acc, bu_gather<NW, U>(a, true, e, end, 1, scanned, fetched));
+                    if (lw_covers(acc, need)) break;
+                }
+                const LW<NW> found = lw_and(acc, need);
+                if (lw_any(found)) {
+                    const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
+                    lw_store<NW>(a.visited, u, nv);
+                    lw_store<NW>(a.nxt, u, found);
+                    ++written;
+                    has_new = true;
+                    if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; mu_delta -= end - beg; }
+                }
+            }
+        }
+        const unsigned nz = __ballot_sync(0xffffffffu, has_new);
+        const unsigned fb = __ballot_sync(0xffffffffu, full_now);
+        bu_store_block_bits(a, b, lane, fullw, nz, fb);
+    }
+    flush_counters(a.ctrl, SLOT_BU_G2, scanned, fetched, examined, written);
+    mu_delta = (long long)warp_sum((ull)mu_delta);
+    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+}
+
+/* Longer rows: a warp owns 32 consecutive vertices and handles 32/G of them at a
+ * time, G threads per vertex.  Degrees are sorted, so the vertices of a warp have
+ * similar row lengths and the warp-uniform inner loop wastes little. */
 template <int NW, int G, int U>
-__global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, int blk_hi) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_sweep_kernel(TravArgs a, int blk_lo, int blk_hi) {
     constexpr int VPI = 32 / G;
     const int lane = threadIdx.x & 31;
     const int sub = lane % G, grp = lane / G;
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
-    const LW<NW> live = lw_from<NW>(a.ctrl->live);
-    const LW<NW> active = lw_from<NW>(a.ctrl->active);
-    ull scanned = 0, fetched = 0, examined = 0, written = 0;
+    unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     long long mu_delta = 0;
 
     for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
@@ -354,11 +404,10 @@ __global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, i
             const int u = base + vi;
             const long long beg = __shfl_sync(0xffffffffu, rp_lo, vi);
             const long long end = __shfl_sync(0xffffffffu, rp_hi, vi);
-            LW<NW> vis = lw_zero<NW>(), need = lw_zero<NW>();
+            LW<NW> need = lw_zero<NW>();
             bool cand = !((fullw >> vi) & 1u) && end > beg;
             if (cand) {
-                vis = lw_load<NW>(a.visited, u);
-                need = lw_andn(live, vis);
+                need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
                 cand = lw_any(need);
             }
             if (cand && sub == 0) ++examined;
@@ -368,21 +417,19 @@ __global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, i
             while (__any_sync(0xffffffffu, go)) {
                 acc = lw_or(acc, bu_gather<NW, U>(a, go, e, end, G, scanned, fetched));
                 e += (long long)G * U;
-                if (G >= 8) { /* early exit: every live lane this vertex misses has been found */
-                    const LW<NW> g = group_or<NW, G>(acc, gmask);
-                    if (lw_covers(g, need)) go = false;
-                }
+                /* early exit: every live lane this vertex misses has been found */
+                if (lw_covers(group_or<NW, G>(acc, gmask), need)) go = false;
                 if (e - sub >= end) go = false;
             }
             const LW<NW> found = lw_and(group_or<NW, G>(acc, gmask), need);
             const bool has_new = cand && lw_any(found);
             bool full_now = false;
             if (has_new && sub == 0) {
-                const LW<NW> nv = lw_or(vis, found);
+                const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
                 lw_store<NW>(a.visited, u, nv);
                 lw_store<NW>(a.nxt, u, found);
                 ++written;
-                if (lw_covers(nv, active)) { full_now = true; mu_delta -= end - beg; }
+                if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; mu_delta -= end - beg; }
             }
             /* leaders' flags -> bits it*VPI .. it*VPI+VPI-1 of the block's bitmap words */
             const bool f_new = __shfl_sync(0xffffffffu, (int)(has_new && sub == 0), (lane % VPI) * G) != 0;
@@ -390,60 +437,69 @@ __global__ void __launch_bounds__(CTA) bu_sweep_kernel(TravArgs a, int blk_lo, i
             nzbits |= __ballot_sync(0xffffffffu, f_new && lane < VPI) << (it * VPI);
             fullbits |= __ballot_sync(0xffffffffu, f_full && lane < VPI) << (it * VPI);
         }
-        if (lane == 0) {
-            a.nxt_nz[b] = nzbits;
-            if (fullbits) a.vis_full[b] = fullw | fullbits;
-        }
+        bu_store_block_bits(a, b, lane, fullw, nzbits, fullbits);
     }
-    flush_counters(a.ctrl, G == 32 ? SLOT_BU_G32 : G == 8 ? SLOT_BU_G8 : SLOT_BU_G2, scanned, fetched, examined, written);
+    flush_counters(a.ctrl, G == 32 ? SLOT_BU_G32 : SLOT_BU_G8, scanned, fetched, examined, written);
     mu_delta = (long long)warp_sum((ull)mu_delta);
     if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
 }
 
-/* Hub rows: one warp per 1024-entry chunk.  Chunks of the same row share what they
- * have found through hub_acc (atomic OR) and stop once the row's need is covered. */
+/* Rows longer than a.seg entries: one thread per segment of a.seg entries, work items
+ * level-major (all first segments, then all second segments, ...), so consecutive
+ * threads work on consecutive vertices (coalesced visited / hub_acc / row_ptr reads)
+ * and the early segments of a row have usually run before its later ones start.
+ * Segments of a row co-operate through hub_acc: a segment first subtracts what earlier
+ * segments already found and skips the row when nothing is left to find. */
 template <int NW, int U>
-__global__ void __launch_bounds__(CTA) bu_heavy_kernel(TravArgs a) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_segment_kernel(TravArgs a) {
     const int lane = threadIdx.x & 31;
-    const LW<NW> live = lw_from<NW>(a.ctrl->live);
-    ull scanned = 0, fetched = 0, examined = 0, written = 0;
-    for (long long c = global_warp(); c < a.n_chunks; c += total_warps()) {
-        int k, u;
-        chunk_lookup(a, c, k, u);
-        if (test_bit(a.vis_full, u)) continue;
-        const LW<NW> need = lw_andn(live, lw_load<NW>(a.visited, u));
-        if (!lw_any(need)) continue;
-        LW<NW> known = lw_load_volatile<NW>(a.hub_acc, u);
-        if (lw_covers(known, need)) continue;
-        const long long beg = a.row_ptr[u] + (long long)k * MSBFS_CHUNK;
-        const long long end = min(beg + (long long)MSBFS_CHUNK, a.row_ptr[u + 1]);
-        if (lane == 0 && k == 0) ++examined;
-        for (long long e = beg + lane; e - lane < end; e += 32ll * U) {
-            const LW<NW> t = bu_gather<NW, U>(a, true, e, end, 32, scanned, fetched);
-            const LW<NW> fresh = lw_andn(lw_and(group_or<NW, 32>(t, 0xffffffffu), need), known);
-            if (lw_any(fresh)) {
-                if (lane == 0) {
-#pragma unroll
-                    for (int i = 0; i < NW; ++i)
-                        if (fresh.w[i]) atomicOr(&a.hub_acc[(long long)u * NW + i], fresh.w[i]);
-                    ++written;
-                }
-                __syncwarp();
-                known = lw_or(lw_load_volatile<NW>(a.hub_acc, u), fresh);
+    unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
+    for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
+        const long long c = c0 + lane;
+        if (c >= a.n_seg_items) continue;
+        int k;
+        {   /* largest k with base[k] <= c0, then walk forward to this thread's item */
+            int lo = 0, hi = a.n_seg_levels;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (a.seg_level_base[mid] <= c0) lo = mid; else hi = mid;
             }
-            if (lw_covers(known, need)) break;
+            k = lo;
+            while (c >= a.seg_level_base[k + 1]) ++k;
+        }
+        const int u = (int)(c - a.seg_level_base[k]);
+        if (test_bit(a.vis_full, u)) continue;
+        LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
+        if (!lw_any(need)) continue;
+        if (k == 0) ++examined;
+        need = lw_andn(need, lw_load_volatile<NW>(a.hub_acc, u));
+        if (!lw_any(need)) continue;
+        const long long beg = a.row_ptr[u] + (long long)k * a.seg;
+        const long long end = min(beg + (long long)a.seg, a.row_ptr[u + 1]);
+        LW<NW> acc = lw_zero<NW>();
+        for (long long e = beg; e < end; e += U) {
+            acc = lw_or(acc, bu_gather<NW, U>(a, true, e, end, 1, scanned, fetched));
+            if (lw_covers(acc, need)) break;
+        }
+        const LW<NW> found = lw_and(acc, need);
+        if (lw_any(found)) {
+#pragma unroll
+            for (int i = 0; i < NW; ++i)
+                if (found.w[i]) atomicOr(&a.hub_acc[(long long)u * NW + i], found.w[i]);
+            ++written;
         }
     }
     flush_counters(a.ctrl, SLOT_BU_HEAVY, scanned, fetched, examined, written);
 }
 
+/* hub_acc -> new frontier for the blocks [0, nblk_hub) handled by bu_segment_kernel */
 template <int NW>
-__global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a) {
+__global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int nblk_hub) {
     const int lane = threadIdx.x & 31;
     const LW<NW> live = lw_from<NW>(a.ctrl->live);
     const LW<NW> active = lw_from<NW>(a.ctrl->active);
     long long mu_delta = 0;
-    for (int b = global_warp(); b < a.blk_heavy; b += total_warps()) {
+    for (int b = global_warp(); b < nblk_hub; b += total_warps()) {
         const int u = (b << 5) + lane;
         const unsigned fullw = a.vis_full[b];
         bool has_new = false, full_now = false;
@@ -543,25 +599,31 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
     csa.init();
     int pending = 0;
     ull nf = 0, mf = 0;
-    for (int b = global_warp(); b < nblk; b += total_warps()) {
-        const int v = (b << 5) + lane;
+    unsigned heavy = 0u;
+    /* two blocks per pass: both bitmap words, then both lane words, are in flight together */
+    for (int b0 = 2 * global_warp(); b0 < nblk; b0 += 2 * total_warps()) {
+        const int b1 = b0 + 1;
+        const bool has1 = b1 < nblk;
         if (MODE == 0) {
-            const unsigned w = a.nxt_nz[b];
-            if (w == 0u) continue;
-            if ((w >> lane) & 1u) {
-                const LW<NW> x = lw_load<NW>(a.nxt, v);
-                csa.add(x.w);
-                ++nf;
-                mf += (ull)(a.row_ptr[v + 1] - a.row_ptr[v]);
-            }
+            const unsigned w0 = a.nxt_nz[b0], w1 = has1 ? a.nxt_nz[b1] : 0u;
+            if ((w0 | w1) == 0u) continue;
+            if ((w0 && b0 < a.blk_heavy) || (w1 && b1 < a.blk_heavy)) heavy = 1u;
+            const bool on0 = (w0 >> lane) & 1u, on1 = (w1 >> lane) & 1u;
+            const int v0 = (b0 << 5) + lane, v1 = (b1 << 5) + lane;
+            LW<NW> x0 = lw_zero<NW>(), x1 = lw_zero<NW>();
+            if (on0) x0 = lw_load<NW>(a.nxt, v0);
+            if (on1) x1 = lw_load<NW>(a.nxt, v1);
+            if (on0) { csa.add(x0.w); ++nf; mf += (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]); }
+            if (on1) { csa.add(x1.w); ++nf; mf += (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]); }
         } else {
-            const ull deg = (ull)(a.row_ptr[v + 1] - a.row_ptr[v]);
-            if ((deg >> degbit) & 1ull) {
-                const LW<NW> x = lw_load<NW>(a.visited, v);
-                csa.add(x.w);
-            }
+            const int v0 = (b0 << 5) + lane, v1 = (b1 << 5) + lane;
+            const ull d0 = (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]);
+            const ull d1 = has1 ? (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]) : 0ull;
+            if ((d0 >> degbit) & 1ull) { const LW<NW> x = lw_load<NW>(a.visited, v0); csa.add(x.w); }
+            if ((d1 >> degbit) & 1ull) { const LW<NW> x = lw_load<NW>(a.visited, v1); csa.add(x.w); }
         }
-        if (++pending == 31) { csa.flush(lane); pending = 0; }
+        pending += 2;
+        if (pending >= 30) { csa.flush(lane); pending = 0; }
     }
     csa.flush(lane);
 #pragma unroll
@@ -579,6 +641,7 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
         nf = warp_sum(nf);
         mf = warp_sum(mf);
         if (lane == 0 && nf) { atomicAdd(&a.ctrl->n_f, nf); atomicAdd(&a.ctrl->m_f, mf); }
+        if (__any_sync(0xffffffffu, heavy != 0u) && lane == 0) a.ctrl->heavy_frontier = 1u;
     }
 }
 
@@ -597,7 +660,7 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz) {
         c->active[j] = m;
     }
     if (j == 0) {
-        c->n_f = 0; c->m_f = 0; c->m_u = nnz;
+        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->heavy_frontier = 0u;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level = -1;
     }
@@ -631,6 +694,8 @@ __global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelV
         verdict->done = (nf == 0ull);
         verdict->next_direction = next;
         verdict->n_f = nf; verdict->m_f = mf; verdict->m_u = mu;
+        verdict->heavy_frontier = (int)c->heavy_frontier;
+        c->heavy_frontier = 0u;
         c->n_f = 0; c->m_f = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level += 1;
@@ -699,7 +764,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
     Launcher L;
     L.h = h;
-    L.grid_cap = h->sm_count * 6;
+    L.grid_cap = h->sm_count * 8;
     TravArgs& a = L.a;
     a.row_ptr = h->d_row_ptr; a.col = h->d_col;
     a.visited = h->d_visited; a.cur = h->d_cur; a.nxt = h->d_nxt; a.acc = h->d_acc; a.hub_acc = h->d_hub_acc;
@@ -708,6 +773,8 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     a.chunk_level_base = h->d_chunk_level_base; a.n_chunk_levels = h->n_chunk_levels; a.n_chunks = h->n_chunks;
     a.n_pad = h->n_pad;
     a.blk_heavy = h->blk_heavy; a.blk_warp = h->blk_warp; a.blk_g8 = h->blk_g8; a.blk_end = h->blk_end;
+    a.seg_level_base = h->d_seg_level_base; a.n_seg_levels = h->n_seg_levels; a.n_seg_items = h->n_seg_items;
+    a.seg = h->seg; a.blk_multi = h->blk_multi;
 
     ull* d_reached = nullptr;
     if (want_reached) {
@@ -744,11 +811,12 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             MSBFS_CUDA(cudaStreamSynchronize(s));
             if (h->h_verdict->done) break;
             const int dir = h->h_verdict->next_direction;
+            const bool heavy_frontier = h->h_verdict->heavy_frontier != 0;
             ++levels;
             if (dir == 1) {
                 ++levels_td;
                 MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
-                if (a.n_chunks > 0)
+                if (a.n_chunks > 0 && heavy_frontier)
                     L.timed(SLOT_TD_HEAVY, [&] { td_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a); });
                 if (a.blk_warp > a.blk_heavy)
                     L.timed(SLOT_TD_G32, [&] {
@@ -765,24 +833,18 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                 L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
             } else {
                 ++levels_bu;
-                if (a.blk_heavy > 0) {
-                    if (a.n_chunks > 0)
-                        L.timed(SLOT_BU_HEAVY, [&] { bu_heavy_kernel<NW, 4><<<L.grid_for_warps(a.n_chunks), CTA, 0, s>>>(a); });
+                if (a.blk_multi > 0) {
+                    if (a.n_seg_items > 0)
+                        L.timed(SLOT_BU_HEAVY, [&] {
+                            bu_segment_kernel<NW, 4><<<L.grid_for_warps((a.n_seg_items + 31) / 32), CTA, 0, s>>>(a);
+                        });
                     L.timed(SLOT_BU_HEAVY_FINALIZE, [&] {
-                        bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_heavy), CTA, 0, s>>>(a);
+                        bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_multi), CTA, 0, s>>>(a, a.blk_multi);
                     });
                 }
-                if (a.blk_warp > a.blk_heavy)
-                    L.timed(SLOT_BU_G32, [&] {
-                        bu_sweep_kernel<NW, 32, 4><<<L.grid_for_warps(a.blk_warp - a.blk_heavy), CTA, 0, s>>>(a, a.blk_heavy, a.blk_warp);
-                    });
-                if (a.blk_g8 > a.blk_warp)
-                    L.timed(SLOT_BU_G8, [&] {
-                        bu_sweep_kernel<NW, 8, 4><<<L.grid_for_warps(a.blk_g8 - a.blk_warp), CTA, 0, s>>>(a, a.blk_warp, a.blk_g8);
-                    });
-                if (a.blk_end > a.blk_g8)
+                if (a.blk_end > a.blk_multi)
                     L.timed(SLOT_BU_G2, [&] {
-                        bu_sweep_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
+                        bu_thread_kernel<NW, 4><<<L.grid_for_warps(a.blk_end - a.blk_multi), CTA, 0, s>>>(a, a.blk_multi, a.blk_end);
                     });
             }
             L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
@@ -828,7 +890,7 @@ int ensure_traversal_buffers(msbfs_handle* h, int nw) {
     MSBFS_CUDA(cudaMalloc(&h->d_cur, word_bytes));
     MSBFS_CUDA(cudaMalloc(&h->d_nxt, word_bytes));
     MSBFS_CUDA(cudaMalloc(&h->d_acc, word_bytes));
-    const size_t hub_bytes = (size_t)std::max(h->blk_heavy * 32, 32) * nw * sizeof(ull);
+    const size_t hub_bytes = (size_t)std::max(h->blk_multi * 32, 32) * nw * sizeof(ull);
     MSBFS_CUDA(cudaMalloc(&h->d_hub_acc, hub_bytes));
     MSBFS_CUDA(cudaMalloc(&h->d_bitmaps, sizeof(unsigned) * 3 * nblk));
     MSBFS_CUDA(cudaMalloc(&h->d_ctrl, sizeof(LevelCtrl)));
@@ -884,7 +946,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0;
     h->level_log.clear();
     static const char* kSlotNames[MSBFS_NUM_SLOTS] = {"td_heavy", "td_expand_g32", "td_expand_g8", "td_expand_g2",
-                                                      "bu_heavy", "bu_sweep_g32", "bu_sweep_g8", "bu_sweep_g2",
+                                                      "bu_segment", "bu_sweep_g32", "bu_sweep_g8", "bu_thread",
                                                       "td_finalize", "bu_heavy_finalize", "count", "bookkeeping"};
     for (int i = 0; i < MSBFS_NUM_SLOTS; ++i) {
         std::memset(&h->slot_profile[i], 0, sizeof h->slot_profile[i]);
