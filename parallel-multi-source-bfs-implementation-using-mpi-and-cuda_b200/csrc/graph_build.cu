@@ -301,7 +301,7 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
     cudaFree(deg_sorted.p); deg_sorted.p = nullptr;
 
     /* 4 + 5. keys -> sort -> col */
-    MSBFS_CUDA(cudaMalloc(&h->d_col, sizeof(int) * (size_t)std::max<int64_t>(nnz, 1)));
+    MSBFS_CUDA(cudaMalloc(&h->d_col, sizeof(int) * (size_t)(nnz + 8))); /* +8: 128-bit loads of the last entries */
     if (nnz > 0) {
         DevBuf k0, k1, tmp3;
         MSBFS_CUDA(k0.alloc(sizeof(unsigned long long) * (size_t)nnz));
