@@ -99,6 +99,28 @@ int msbfs_download_sums(msbfs_t* h, int64_t* out_sums, int32_t count);
  * edges = half of it).  Runs an extra device pass when called. */
 int msbfs_reached_entries(msbfs_t* h, int64_t* out_entries, int32_t count);
 
+/* No counterpart in the reference.  F of up to 64 groups on a graph of at most 65,536
+ * vertices, computed without allocating: for callers that may not call cudaMalloc or
+ * cudaFree where this runs (a latency-critical loop that cannot afford the device-wide
+ * stall an allocation may cause, a host application whose memory pool owns the whole
+ * GPU, a process held to a memory budget fixed at start-up).  The traversal state lives
+ * in a 1.5 MiB __device__ array inside the library (every GPU that loads the library
+ * holds it until exit); larger inputs are refused with MSBFS_ERR_RANGE — use msbfs_run.
+ *   inputs   CSR of the graph in the caller's own vertex ids, both directions stored
+ *            (d_row_offsets int64[n + 1], d_col_indices int32), groups as in msbfs_run
+ *            (d_group_offsets int64[num_groups + 1] starting at 0, d_sources int32);
+ *   output   d_out_sums int64[num_groups];
+ *   all five are device pointers on the CURRENT device; the work is queued on
+ *   `cuda_stream` (a cudaStream_t, NULL = default stream) and the sums are complete when
+ *   that stream reaches the end of it — the call itself does not wait.
+ * The first call on each device also looks up the array's device address; make that
+ * first call before any stream capture.  All calls share the one array (each call
+ * clears the part it uses before reading it), so calls that overlap on the same GPU —
+ * different streams or threads — race with each other: serialise them. */
+int msbfs_small_run_noalloc(int32_t n, const int64_t* d_row_offsets, const int32_t* d_col_indices,
+                            int32_t num_groups, const int64_t* d_group_offsets, const int32_t* d_sources,
+                            int64_t* d_out_sums, void* cuda_stream);
+
 /* ------------------------------------------------------------- reduction -- */
 
 /* Replaces the argmin, main.cu:379-397, over a full array: first F >= 0 seeds,

@@ -93,6 +93,7 @@ SIGNATURES = {
     "msbfs_run_resident": (C.c_int, [C.c_void_p]),
     "msbfs_download_sums": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "msbfs_reached_entries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "msbfs_small_run_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "msbfs_argmin": (C.c_int, [C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_argmin_packed": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_uint64)]),
     "msbfs_unpack_argmin": (C.c_int, [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
