@@ -73,6 +73,7 @@ struct LevelCtrl {
     int level;                                 /* depth being expanded (-1 = injection)       */
     int log_pos;
     unsigned heavy_frontier;                   /* new frontier touches a chunked (hub) row    */
+    int last_done, last_next;                  /* device-side copy of the verdict (streak kernel) */
     /* per-kernel accumulators over a whole run (roofline accounting), see KernelSlot */
     unsigned long long k_scanned[MSBFS_NUM_SLOTS], k_fetched[MSBFS_NUM_SLOTS], k_examined[MSBFS_NUM_SLOTS],
         k_written[MSBFS_NUM_SLOTS];
@@ -83,7 +84,7 @@ struct LevelVerdict {
     int32_t done;
     int32_t next_direction;
     int32_t heavy_frontier;
-    int32_t pad_;
+    int32_t streak_levels;  /* levels run by the last persistent top-down kernel */
     uint64_t n_f, m_f;
     int64_t m_u;
 };
@@ -137,6 +138,7 @@ struct msbfs_handle {
     int n_seg_levels = 0, blk_multi = 0, seg = 256;
     long long n_seg_items = 0;
     bool has_graph = false;
+    unsigned max_degree = 0;
     double build_ms = 0.0;
 
     /* traversal state */
@@ -163,6 +165,8 @@ struct msbfs_handle {
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
     int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
     int opt_mid_variant = 0;                   /* experiment knob: kernel shape of the middle bin */
+    int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
+    int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_seg = 256;                         /* bottom-up segment length (next graph load)      */
     long long opt_alpha = 8;
 

@@ -273,6 +273,7 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
         MSBFS_CUDA(cudaStreamSynchronize(s));
         const int nblk = n_pad / 32;
         h->seg = seg;
+        h->max_degree = maxdeg;
         h->blk_multi = std::min(nblk, (first_short + 31) / 32);
         const int n_multi = std::min(h->blk_multi * 32, n_active);
         const int levels = n_multi > 0 ? (int)(((long long)maxdeg + seg - 1) / seg) : 0;

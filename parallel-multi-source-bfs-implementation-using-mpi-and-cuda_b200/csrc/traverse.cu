@@ -33,8 +33,12 @@
  */
 #include "engine.h"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cstring>
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -695,8 +699,8 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz) {
 /* F(j) += (level + 1) * count(j)  (the reference's sum of distances, main.cu:81-87,
  * taken level by level), live lanes, and the direction of the next level.
  * `direction` is what the level just finished used (0 = injection). */
-__global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
-                                int direction, long long alpha, int force_direction) {
+__device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
+                                              int direction, long long alpha, int force_direction) {
     const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
     const ull cnt = c->cnt[j];
     c->sums[j] += (ull)(c->level + 1) * cnt;
@@ -721,10 +725,199 @@ __global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelV
         verdict->next_direction = next;
         verdict->n_f = nf; verdict->m_f = mf; verdict->m_u = mu;
         verdict->heavy_frontier = (int)c->heavy_frontier;
+        c->last_done = (nf == 0ull);
+        c->last_next = next;
         c->heavy_frontier = 0u;
         c->n_f = 0; c->m_f = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level += 1;
+        __threadfence_system();
+    }
+}
+
+__global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
+                                int direction, long long alpha, int force_direction) {
+    epilogue_body(c, log, log_cap, verdict, direction, alpha, force_direction);
+}
+
+/* -------------------------------------------- top-down streak (persistent) --- */
+
+/* High-diameter, low-degree graphs (road-like lattices) run thousands of levels whose
+ * frontiers are small: the cost is then launches and host round trips, not bytes.  This
+ * cooperative kernel keeps one grid resident and runs consecutive top-down levels —
+ * expand, finalize + per-lane count, epilogue — separated by grid-wide barriers, until
+ * the BFS is done or the direction heuristic asks for a bottom-up level.  Used only when
+ * every row is short (max degree <= STREAK_MAX_DEG), so a frontier vertex is one thread.
+ * On return the host finds ctrl / verdict exactly as after a normal epilogue, plus the
+ * number of levels run (the frontier buffers have swapped that many times). */
+constexpr int STREAK_MAX_DEG = 32;
+
+/* A warp takes a tile of 32 bitmap words (1024 vertices, one coalesced 128-byte read) and
+ * hands the set bits out densely: round r gives lane j the (32 r + j)-th set bit of the
+ * tile.  With a few frontier vertices per 32-vertex block this keeps all 32 lanes busy
+ * and 32 independent load chains in flight instead of two or three. */
+struct TileBits {
+    unsigned w;      /* this lane's bitmap word */
+    int excl, total; /* set bits in the lanes below / in the whole tile */
+    __device__ __forceinline__ void load(unsigned word, int lane) {
+        w = word;
+        const int cnt = __popc(w);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        excl = incl - cnt;
+        total = __shfl_sync(0xffffffffu, incl, 31);
+    }
+    /* vertex offset inside the tile (0..1023) of set bit number `rank`; all lanes must call */
+    __device__ __forceinline__ int select(int rank) const {
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int cand = lo + step;
+            const int e = __shfl_sync(0xffffffffu, excl, cand & 31);
+            if (cand < 32 && e <= rank) lo = cand;
+        }
+        const unsigned wi = __shfl_sync(0xffffffffu, w, lo);
+        const int ei = __shfl_sync(0xffffffffu, excl, lo);
+        const int r = rank - ei;
+        const int bit = (r >= 0 && r < __popc(wi)) ? (int)__fns(wi, 0, r + 1) : 0;
+        return (lo << 5) + bit;
+    }
+};
+
+template <int NW>
+__global__ void __launch_bounds__(CTA, 3) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
+                                                           long long alpha, int force_direction, int max_levels) {
+    cg::grid_group grid = cg::this_grid();
+    constexpr int NC = 2 * NW;
+    __shared__ unsigned s_cnt[64 * NW];
+    __shared__ ull s_ctr[6]; /* scanned, fetched, examined, written, nf, mf */
+    __shared__ long long s_mu;
+    __shared__ unsigned s_flags; /* bit 0: this block saw new frontier words */
+    const int lane = threadIdx.x & 31;
+    const int nblk = a.n_pad >> 5;
+    const int ntiles = (nblk + 31) >> 5;
+    int levels_run = 0;
+
+    for (;;) {
+        for (int i = threadIdx.x; i < 64 * NW; i += CTA) s_cnt[i] = 0u;
+        if (threadIdx.x < 6) s_ctr[threadIdx.x] = 0ull;
+        if (threadIdx.x == 0) { s_mu = 0; s_flags = 0u; }
+        __syncthreads();
+
+        /* ---- expand: one thread per frontier vertex; consumed bitmap words are cleared so
+         *      that this buffer is a clean nxt_nz two levels from now */
+        {
+            ull scanned = 0, fetched = 0, examined = 0, written = 0;
+            for (int t = global_warp(); t < ntiles; t += total_warps()) {
+                const int b = (t << 5) + lane;
+                unsigned word = 0u;
+                if (b < nblk) {
+                    word = a.cur_nz[b];
+                    if (word) a.cur_nz[b] = 0u;
+                }
+                TileBits tb;
+                tb.load(word, lane);
+                for (int r0 = 0; r0 < tb.total; r0 += 32) {
+                    const int off = tb.select(r0 + lane);
+                    if (r0 + lane < tb.total) {
+                        const int v = (t << 10) + off;
+                        const LW<NW> f = lw_load<NW>(a.cur, v);
+                        ++examined;
+                        td_push<NW, 4>(a, f, a.row_ptr[v], a.row_ptr[v + 1], 1, scanned, fetched, written);
+                    }
+                }
+            }
+            scanned = warp_sum(scanned); fetched = warp_sum(fetched);
+            examined = warp_sum(examined); written = warp_sum(written);
+            if (lane == 0 && (scanned | examined)) {
+                atomicAdd(&s_ctr[0], scanned); atomicAdd(&s_ctr[1], fetched);
+                atomicAdd(&s_ctr[2], examined); atomicAdd(&s_ctr[3], written);
+            }
+        }
+        grid.sync();
+
+        /* ---- finalize + count */
+        {
+            Csa<NC> csa;
+            csa.init();
+            int pending = 0;
+            ull nf = 0, mf = 0;
+            long long mu_delta = 0;
+            bool warp_any = false;
+            for (int t = global_warp(); t < ntiles; t += total_warps()) {
+                const int b = (t << 5) + lane;
+                TileBits tb;
+                tb.load(b < nblk ? a.nxt_nz[b] : 0u, lane);
+                if (tb.total == 0) continue;
+                warp_any = true;
+                for (int r0 = 0; r0 < tb.total; r0 += 32) {
+                    const int off = tb.select(r0 + lane);
+                    if (r0 + lane < tb.total) {
+                        const int v = (t << 10) + off;
+                        const LW<NW> x = lw_load<NW>(a.acc, v);
+                        lw_store<NW>(a.acc, v, lw_zero<NW>());
+                        const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
+                        lw_store<NW>(a.visited, v, nv);
+                        lw_store<NW>(a.nxt, v, x);
+                        csa.add(x.w);
+                        ++nf;
+                        const long long deg = a.row_ptr[v + 1] - a.row_ptr[v];
+                        mf += (ull)deg;
+                        if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) {
+                            mu_delta -= deg;
+                            atomicOr(&a.vis_full[v >> 5], 1u << (v & 31));
+                        }
+                    }
+                    if (++pending == 31) { csa.flush(lane); pending = 0; }
+                }
+            }
+            if (warp_any) {
+                csa.flush(lane);
+#pragma unroll
+                for (int c = 0; c < NC; ++c)
+                    if (csa.cnt[c]) atomicAdd(&s_cnt[c * 32 + lane], csa.cnt[c]);
+                nf = warp_sum(nf); mf = warp_sum(mf);
+                mu_delta = (long long)warp_sum((ull)mu_delta);
+                if (lane == 0) {
+                    atomicAdd(&s_ctr[4], nf); atomicAdd(&s_ctr[5], mf);
+                    if (mu_delta) atomicAdd((ull*)&s_mu, (ull)mu_delta);
+                    atomicOr(&s_flags, 1u);
+                }
+            }
+        }
+        __syncthreads();
+        if (s_flags & 1u)
+            for (int i = threadIdx.x; i < 64 * NW; i += CTA)
+                if (s_cnt[i]) atomicAdd(&a.ctrl->cnt[i], (ull)s_cnt[i]);
+        if (threadIdx.x == 0) {
+            if (s_ctr[0]) { atomicAdd(&a.ctrl->scanned, s_ctr[0]); atomicAdd(&a.ctrl->k_scanned[SLOT_TD_G2], s_ctr[0]); }
+            if (s_ctr[1]) { atomicAdd(&a.ctrl->words_fetched, s_ctr[1]); atomicAdd(&a.ctrl->k_fetched[SLOT_TD_G2], s_ctr[1]); }
+            if (s_ctr[2]) { atomicAdd(&a.ctrl->examined, s_ctr[2]); atomicAdd(&a.ctrl->k_examined[SLOT_TD_G2], s_ctr[2]); }
+            if (s_ctr[3]) { atomicAdd(&a.ctrl->words_written, s_ctr[3]); atomicAdd(&a.ctrl->k_written[SLOT_TD_G2], s_ctr[3]); }
+            if (s_ctr[4]) { atomicAdd(&a.ctrl->n_f, s_ctr[4]); atomicAdd(&a.ctrl->m_f, s_ctr[5]); }
+            if (s_mu) atomicAdd((ull*)&a.ctrl->m_u, (ull)s_mu);
+        }
+        __threadfence();
+        grid.sync();
+
+        /* ---- epilogue by block 0, verdict read by everyone */
+        if (blockIdx.x == 0) epilogue_body(a.ctrl, log, log_cap, verdict, 1, alpha, force_direction);
+        __threadfence();
+        grid.sync();
+        ++levels_run;
+        const volatile LevelCtrl* vc = a.ctrl;
+        const bool stop = vc->last_done || vc->last_next != 1 || levels_run >= max_levels;
+        /* the frontier buffers trade places */
+        ull* t = a.cur; a.cur = a.nxt; a.nxt = t;
+        unsigned* tb = a.cur_nz; a.cur_nz = a.nxt_nz; a.nxt_nz = tb;
+        if (stop) break;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        verdict->streak_levels = levels_run;
         __threadfence_system();
     }
 }
@@ -802,6 +995,15 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     a.seg_level_base = h->d_seg_level_base; a.n_seg_levels = h->n_seg_levels; a.n_seg_items = h->n_seg_items;
     a.seg = h->seg; a.blk_multi = h->blk_multi;
 
+    /* persistent top-down kernel: only when every row is short and the device can co-schedule the grid */
+    int streak_grid = 0;
+    if (h->opt_streak && h->max_degree <= (unsigned)STREAK_MAX_DEG) {
+        int coop = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device);
+        if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, td_streak_kernel<NW>, CTA, 0) == cudaSuccess && per_sm > 0)
+            streak_grid = per_sm * h->sm_count;
+    }
+
     ull* d_reached = nullptr;
     if (want_reached) {
         MSBFS_CUDA(cudaMalloc(&d_reached, sizeof(ull) * MSBFS_MAX_LANES));
@@ -839,6 +1041,25 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             const int dir = h->h_verdict->next_direction;
             const bool heavy_frontier = h->h_verdict->heavy_frontier != 0;
             ++levels;
+            if (dir == 1 && streak_grid > 0) {
+                /* short-row graph: stay on the device for as many top-down levels as it takes */
+                MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
+                long long alpha = h->opt_alpha;
+                int force = h->opt_direction, max_levels = h->opt_streak_levels;
+                void* args[] = {&a, &h->d_log, &h->log_cap, &h->h_verdict, &alpha, &force, &max_levels};
+                cudaError_t ce = cudaSuccess;
+                L.timed(SLOT_TD_G2, [&] {
+                    ce = cudaLaunchCooperativeKernel((const void*)td_streak_kernel<NW>, dim3(streak_grid), dim3(CTA), args, 0, s);
+                });
+                if (ce != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "cooperative launch failed: %s", cudaGetErrorString(ce));
+                MSBFS_CUDA(cudaStreamSynchronize(s));
+                const int run = h->h_verdict->streak_levels;
+                levels += run - 1;
+                levels_td += run;
+                /* the kernel swapped the frontier buffers `run` times; the loop head swaps once more */
+                if (run % 2 == 0) { std::swap(a.cur, a.nxt); std::swap(a.cur_nz, a.nxt_nz); }
+                continue;
+            }
             if (dir == 1) {
                 ++levels_td;
                 MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));

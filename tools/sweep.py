@@ -1,13 +1,13 @@
 """Experiment helper (not part of the product): run bench.py with several option sets and
 print one summary line each.  usage: python tools_sweep.py WORKLOAD "k=v,k=v" "k=v" ..."""
-import json, subprocess, sys
+import json, os, subprocess, sys
 wl = sys.argv[1]
 for spec in sys.argv[2:]:
     opts = []
     for kv in spec.split(","):
         if kv and kv != "base":
             opts += ["--opt", kv]
-    res = subprocess.run([sys.executable, "bench.py", "--workload", wl, "--steps", "2", "--warmup", "1", "--no-cpu"] + opts,
+    res = subprocess.run([sys.executable, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"), "--workload", wl, "--steps", "2", "--warmup", "1", "--no-cpu"] + opts,
                          capture_output=True, text=True)
     try:
         d = json.loads(res.stdout.strip().splitlines()[-1])
