@@ -161,8 +161,6 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "seg")) {
         if (value < 8 || value > (1 << 20)) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
         h->opt_seg = (int)value;
-    } else if (!std::strcmp(key, "mid_variant")) {
-        h->opt_mid_variant = (int)value;
     } else if (!std::strcmp(key, "profile")) {
         h->opt_profile = value != 0;
     } else {

@@ -164,7 +164,6 @@ struct msbfs_handle {
     /* options */
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
     int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
-    int opt_mid_variant = 0;                   /* experiment knob: kernel shape of the middle bin */
     int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_seg = 256;                         /* bottom-up segment length (next graph load)      */

@@ -22,11 +22,13 @@
  *   td_expand   top-down: frontier vertices push their word to neighbours (RED.OR)
  *   td_heavy    same for chunked hub rows
  *   td_finalize acc -> new frontier word, visited |= new
- *   bu_sweep    bottom-up: every not-yet-full vertex ORs its neighbours' frontier
- *               words, stops as soon as all live lanes are found; fused finalize
- *   bu_heavy    same for hub rows, one warp per 1024-entry chunk, chunks of a row
- *               co-operate through hub_acc
- *   bu_heavy_finalize
+ *   bu_thread   bottom-up, rows of at most `seg` entries: one thread per not-yet-full
+ *               vertex ORs its neighbours' frontier words and stops as soon as all the
+ *               live lanes it misses are found; fused finalize
+ *   bu_segment  bottom-up, longer rows: one thread per `seg`-entry segment, level-major,
+ *               segments of a row co-operate through hub_acc
+ *   bu_heavy_finalize  hub_acc -> new frontier words of the long rows
+ *   td_streak   persistent cooperative top-down loop for short-row (road-like) graphs
  *   count       positional popcount of the new frontier words (per-lane counts)
  *               with bit-sliced carry-save counters and warp bit-matrix transposes
  *   epilogue    F += (L+1) x counts, live-lane mask, direction for the next level
@@ -297,34 +299,6 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
 
 /* ------------------------------------------------------------ bottom-up --- */
 
-/* One outer step of a bottom-up scan: up to U entries per thread, staged so that
- * the col loads, the frontier-bitmap tests and the frontier-word loads of the U
- * entries are each issued back to back.  Returns the OR of the fetched words. */
-template <int NW, int U>
-__device__ __forceinline__ LW<NW> bu_gather(const TravArgs& a, bool go, long long e, long long end, int stride,
-                                            unsigned& scanned, unsigned& fetched) {
-    int v[U];
-    bool ok[U];
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-        const long long ee = e + (long long)k * stride;
-        ok[k] = go && ee < end;
-        v[k] = ok[k] ? __ldg(a.col + ee) : 0;
-    }
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-        scanned += ok[k];
-        ok[k] = ok[k] && test_bit(a.cur_nz, v[k]);
-    }
-    LW<NW> t = lw_zero<NW>();
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-        if (ok[k]) t = lw_or(t, lw_load<NW>(a.cur, v[k]));
-        fetched += ok[k];
-    }
-    return t;
-}
-
 /* Four consecutive col entries with one 128-bit load (e4 is a multiple of 4, so the
  * address is 16-byte aligned; entries outside [beg, end) are masked).  A thread that
  * walks its own row this way touches each 128-byte line of col with 8 requests instead
@@ -402,74 +376,6 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravA
         bu_store_block_bits(a, b, lane, fullw, nz, fb);
     }
     flush_counters(a.ctrl, SLOT_BU_G2, scanned, fetched, examined, written);
-    mu_delta = (long long)warp_sum((ull)mu_delta);
-    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
-}
-
-/* Longer rows: a warp owns 32 consecutive vertices and handles 32/G of them at a
- * time, G threads per vertex.  Degrees are sorted, so the vertices of a warp have
- * similar row lengths and the warp-uniform inner loop wastes little. */
-template <int NW, int G, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_sweep_kernel(TravArgs a, int blk_lo, int blk_hi) {
-    constexpr int VPI = 32 / G;
-    const int lane = threadIdx.x & 31;
-    const int sub = lane % G, grp = lane / G;
-    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
-    unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
-    long long mu_delta = 0;
-
-    for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
-        const int base = b << 5;
-        const unsigned fullw = a.vis_full[b];
-        if (fullw == 0xffffffffu) {
-            if (lane == 0) a.nxt_nz[b] = 0u;
-            continue;
-        }
-        /* row_ptr tile of the block, one coalesced load per lane, handed out by shuffle */
-        const long long rp_lo = a.row_ptr[base + lane], rp_hi = a.row_ptr[base + lane + 1];
-        unsigned nzbits = 0u, fullbits = 0u;
-#pragma unroll 1
-        for (int it = 0; it < G; ++it) {
-            const int vi = it * VPI + grp;
-            const int u = base + vi;
-            const long long beg = __shfl_sync(0xffffffffu, rp_lo, vi);
-            const long long end = __shfl_sync(0xffffffffu, rp_hi, vi);
-            LW<NW> need = lw_zero<NW>();
-            bool cand = !((fullw >> vi) & 1u) && end > beg;
-            if (cand) {
-                need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
-                cand = lw_any(need);
-            }
-            if (cand && sub == 0) ++examined;
-            LW<NW> acc = lw_zero<NW>();
-            bool go = cand;
-            long long e = beg + sub;
-            while (__any_sync(0xffffffffu, go)) {
-                acc = lw_or(acc, bu_gather<NW, U>(a, go, e, end, G, scanned, fetched));
-                e += (long long)G * U;
-                /* early exit: every live lane this vertex misses has been found */
-                if (lw_covers(group_or<NW, G>(acc, gmask), need)) go = false;
-                if (e - sub >= end) go = false;
-            }
-            const LW<NW> found = lw_and(group_or<NW, G>(acc, gmask), need);
-            const bool has_new = cand && lw_any(found);
-            bool full_now = false;
-            if (has_new && sub == 0) {
-                const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
-                lw_store<NW>(a.visited, u, nv);
-                lw_store<NW>(a.nxt, u, found);
-                ++written;
-                if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; mu_delta -= end - beg; }
-            }
-            /* leaders' flags -> bits it*VPI .. it*VPI+VPI-1 of the block's bitmap words */
-            const bool f_new = __shfl_sync(0xffffffffu, (int)(has_new && sub == 0), (lane % VPI) * G) != 0;
-            const bool f_full = __shfl_sync(0xffffffffu, (int)full_now, (lane % VPI) * G) != 0;
-            nzbits |= __ballot_sync(0xffffffffu, f_new && lane < VPI) << (it * VPI);
-            fullbits |= __ballot_sync(0xffffffffu, f_full && lane < VPI) << (it * VPI);
-        }
-        bu_store_block_bits(a, b, lane, fullw, nzbits, fullbits);
-    }
-    flush_counters(a.ctrl, G == 32 ? SLOT_BU_G32 : SLOT_BU_G8, scanned, fetched, examined, written);
     mu_delta = (long long)warp_sum((ull)mu_delta);
     if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
 }
@@ -601,6 +507,24 @@ template <int NC> struct Csa {
             }
         }
     }
+    /* two words at once: a full adder (3-input XOR + majority, one LOP3 each) folds both
+     * into slice 0, then a single carry ripples up — half the work of two add() calls */
+    __device__ __forceinline__ void add2(const ull* w0, const ull* w1) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const unsigned x = (unsigned)(w0[c >> 1] >> ((c & 1) * 32));
+            const unsigned y = (unsigned)(w1[c >> 1] >> ((c & 1) * 32));
+            const unsigned t0 = sl[0][c];
+            sl[0][c] = t0 ^ x ^ y;
+            unsigned carry = (t0 & x) | (t0 & y) | (x & y);
+#pragma unroll
+            for (int s = 1; s < K; ++s) {
+                const unsigned t = sl[s][c] & carry;
+                sl[s][c] ^= carry;
+                carry = t;
+            }
+        }
+    }
     /* warp-collective */
     __device__ __forceinline__ void flush(int lane) {
 #pragma unroll
@@ -643,8 +567,9 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
             LW<NW> x0 = lw_zero<NW>(), x1 = lw_zero<NW>();
             if (on0) x0 = lw_load<NW>(a.nxt, v0);
             if (on1) x1 = lw_load<NW>(a.nxt, v1);
-            if (on0) { csa.add(x0.w); ++nf; mf += (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]); }
-            if (on1) { csa.add(x1.w); ++nf; mf += (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]); }
+            csa.add2(x0.w, x1.w); /* a word that is off is zero and adds nothing */
+            if (on0) { ++nf; mf += (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]); }
+            if (on1) { ++nf; mf += (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]); }
         } else {
             const int v0 = (b0 << 5) + lane, v1 = (b1 << 5) + lane;
             const ull d0 = (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]);
@@ -789,10 +714,9 @@ struct TileBits {
 };
 
 template <int NW>
-__global__ void __launch_bounds__(CTA, 3) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
+__global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
                                                            long long alpha, int force_direction, int max_levels) {
     cg::grid_group grid = cg::this_grid();
-    constexpr int NC = 2 * NW;
     __shared__ unsigned s_cnt[64 * NW];
     __shared__ ull s_ctr[6]; /* scanned, fetched, examined, written, nf, mf */
     __shared__ long long s_mu;
@@ -840,46 +764,65 @@ __global__ void __launch_bounds__(CTA, 3) td_streak_kernel(TravArgs a, LevelLog*
         }
         grid.sync();
 
-        /* ---- finalize + count */
+        /* ---- finalize + count.  Two rounds (64 touched vertices) per pass so that four
+         *      independent word loads per lane are in flight before the first store; lanes are
+         *      counted bit by bit in shared memory (words of a road-like frontier carry few
+         *      lanes), which keeps the kernel at 64 registers. */
         {
-            Csa<NC> csa;
-            csa.init();
-            int pending = 0;
             ull nf = 0, mf = 0;
             long long mu_delta = 0;
             bool warp_any = false;
+            const LW<NW> active = lw_from<NW>(a.ctrl->active);
             for (int t = global_warp(); t < ntiles; t += total_warps()) {
                 const int b = (t << 5) + lane;
                 TileBits tb;
                 tb.load(b < nblk ? a.nxt_nz[b] : 0u, lane);
                 if (tb.total == 0) continue;
                 warp_any = true;
-                for (int r0 = 0; r0 < tb.total; r0 += 32) {
-                    const int off = tb.select(r0 + lane);
-                    if (r0 + lane < tb.total) {
-                        const int v = (t << 10) + off;
-                        const LW<NW> x = lw_load<NW>(a.acc, v);
-                        lw_store<NW>(a.acc, v, lw_zero<NW>());
-                        const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
-                        lw_store<NW>(a.visited, v, nv);
-                        lw_store<NW>(a.nxt, v, x);
-                        csa.add(x.w);
+                for (int r0 = 0; r0 < tb.total; r0 += 64) {
+                    int v[2];
+                    bool ok[2];
+                    LW<NW> x[2], vis[2];
+                    long long deg[2];
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int rank = r0 + 32 * q + lane;
+                        const int off = tb.select(rank);
+                        ok[q] = rank < tb.total;
+                        v[q] = (t << 10) + off;
+                    }
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        x[q] = ok[q] ? lw_load<NW>(a.acc, v[q]) : lw_zero<NW>();
+                        vis[q] = ok[q] ? lw_load<NW>(a.visited, v[q]) : lw_zero<NW>();
+                        deg[q] = ok[q] ? (a.row_ptr[v[q] + 1] - a.row_ptr[v[q]]) : 0;
+                    }
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        if (!ok[q]) continue;
+                        lw_store<NW>(a.acc, v[q], lw_zero<NW>());
+                        const LW<NW> nv = lw_or(vis[q], x[q]);
+                        lw_store<NW>(a.visited, v[q], nv);
+                        lw_store<NW>(a.nxt, v[q], x[q]);
+#pragma unroll
+                        for (int i = 0; i < NW; ++i) {
+                            ull bits = x[q].w[i];
+                            while (bits) {
+                                const int j = __ffsll((long long)bits) - 1;
+                                bits &= bits - 1ull;
+                                atomicAdd(&s_cnt[i * 64 + j], 1u);
+                            }
+                        }
                         ++nf;
-                        const long long deg = a.row_ptr[v + 1] - a.row_ptr[v];
-                        mf += (ull)deg;
-                        if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) {
-                            mu_delta -= deg;
-                            atomicOr(&a.vis_full[v >> 5], 1u << (v & 31));
+                        mf += (ull)deg[q];
+                        if (lw_covers(nv, active)) {
+                            mu_delta -= deg[q];
+                            atomicOr(&a.vis_full[v[q] >> 5], 1u << (v[q] & 31));
                         }
                     }
-                    if (++pending == 31) { csa.flush(lane); pending = 0; }
                 }
             }
             if (warp_any) {
-                csa.flush(lane);
-#pragma unroll
-                for (int c = 0; c < NC; ++c)
-                    if (csa.cnt[c]) atomicAdd(&s_cnt[c * 32 + lane], csa.cnt[c]);
                 nf = warp_sum(nf); mf = warp_sum(mf);
                 mu_delta = (long long)warp_sum((ull)mu_delta);
                 if (lane == 0) {
@@ -1193,7 +1136,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0;
     h->level_log.clear();
     static const char* kSlotNames[MSBFS_NUM_SLOTS] = {"td_heavy", "td_expand_g32", "td_expand_g8", "td_expand_g2",
-                                                      "bu_segment", "bu_sweep_g32", "bu_sweep_g8", "bu_thread",
+                                                      "bu_segment", "(unused)", "(unused)", "bu_thread",
                                                       "td_finalize", "bu_heavy_finalize", "count", "bookkeeping"};
     for (int i = 0; i < MSBFS_NUM_SLOTS; ++i) {
         std::memset(&h->slot_profile[i], 0, sizeof h->slot_profile[i]);
