@@ -63,6 +63,29 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# The driver reads ONE JSON line from stdout.  Libraries (NCCL's version banner, torchrun
+# notices) may print to fd 1, so fd 1 is pointed at stderr for the whole run and the result
+# line goes to a private duplicate of the original stdout.
+_RESULT_FD = None
+
+
+def claim_stdout():
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -221,7 +244,7 @@ def run_reference_arm(args, wl, rank):
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": cores_used, "kind": kind_s, "sample": sample_desc},
         "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def make_edges_host(pkg, wl, kind):
@@ -464,7 +487,7 @@ def run_ours(args, wl, rank, local_rank, world):
         "cpu_baseline": cpu,
         "parity_sample": parity,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -486,6 +509,7 @@ def main():
     ap.add_argument("--alpha", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=0)
     args = ap.parse_args()
+    claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
         log("note: fewer than 3 warm-up steps requested; the timing rules ask for >= 3")
     rank, local_rank, world = dist_env()
