@@ -299,30 +299,62 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
 
 /* ------------------------------------------------------------ bottom-up --- */
 
-/* Four consecutive col entries with one 128-bit load (e4 is a multiple of 4, so the
- * address is 16-byte aligned; entries outside [beg, end) are masked).  A thread that
- * walks its own row this way touches each 128-byte line of col with 8 requests instead
- * of 32 — the L1 wavefront count, not DRAM, bounds the sparse-frontier levels. */
+/* Bottom-up scan of one row segment [beg, end) by one thread, software-pipelined.
+ * col is read four entries at a time with one 128-bit load (the group index is a multiple
+ * of 4, so the address is 16-byte aligned; entries outside [beg, end) are masked) — a
+ * thread walking its own row touches each 128-byte line of col with 8 requests instead of
+ * 32.  While the lane words of group i are in flight, the col entries and the
+ * frontier-bitmap words of group i+1 are already being fetched, so an iteration costs one
+ * memory latency (the words) instead of three chained ones (col -> bitmap -> word): these
+ * kernels are bound by latency x occupancy, not by bytes (ncu r1f).  Stops as soon as
+ * every lane in `need` has been found. */
 template <int NW>
-__device__ __forceinline__ LW<NW> bu_gather4(const TravArgs& a, long long e4, long long beg, long long end,
-                                             unsigned& scanned, unsigned& fetched) {
-    const int4 c = __ldg(reinterpret_cast<const int4*>(a.col + e4));
-    const int v[4] = {c.x, c.y, c.z, c.w};
-    bool ok[4];
+__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, long long beg, long long end, const LW<NW>& need,
+                                              unsigned& scanned, unsigned& fetched) {
+    LW<NW> acc = lw_zero<NW>();
+    long long e4 = beg & ~3ll;
+    int4 c = __ldg(reinterpret_cast<const int4*>(a.col + e4));
+    unsigned m = 0u; /* bit k: entry e4 + k belongs to the segment */
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        ok[k] = (e4 + k >= beg) && (e4 + k < end);
-        scanned += ok[k];
+    for (int k = 0; k < 4; ++k) m |= (unsigned)((e4 + k >= beg) && (e4 + k < end)) << k;
+    unsigned bw[4];
+    {
+        const int v[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) bw[k] = ((m >> k) & 1u) ? a.cur_nz[v[k] >> 5] : 0u;
     }
+    for (;;) {
+        const long long e4n = e4 + 4;
+        const bool more = e4n < end;
+        int4 cn = make_int4(0, 0, 0, 0);
+        if (more) cn = __ldg(reinterpret_cast<const int4*>(a.col + e4n));
+        const int v[4] = {c.x, c.y, c.z, c.w};
+        LW<NW> t = lw_zero<NW>();
 #pragma unroll
-    for (int k = 0; k < 4; ++k) ok[k] = ok[k] && test_bit(a.cur_nz, v[k]);
-    LW<NW> t = lw_zero<NW>();
+        for (int k = 0; k < 4; ++k) {
+            const bool in = (m >> k) & 1u;
+            const bool hit = in && ((bw[k] >> (v[k] & 31)) & 1u);
+            scanned += in;
+            fetched += hit;
+            if (hit) t = lw_or(t, lw_load<NW>(a.cur, v[k]));
+        }
+        unsigned mn = 0u, bwn[4] = {0u, 0u, 0u, 0u};
+        if (more) {
+            const int vn[4] = {cn.x, cn.y, cn.z, cn.w};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        if (ok[k]) t = lw_or(t, lw_load<NW>(a.cur, v[k]));
-        fetched += ok[k];
+            for (int k = 0; k < 4; ++k) {
+                const bool in = e4n + k < end;
+                mn |= (unsigned)in << k;
+                bwn[k] = in ? a.cur_nz[vn[k] >> 5] : 0u;
+            }
+        }
+        acc = lw_or(acc, t);
+        if (!more || lw_covers(acc, need)) break;
+        c = cn; m = mn; e4 = e4n;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) bw[k] = bwn[k];
     }
-    return t;
+    return acc;
 }
 
 /* The block's result bits: nxt_nz is fully rewritten every bottom-up level. */
@@ -355,11 +387,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravA
             const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
             if (lw_any(need)) {
                 ++examined;
-                LW<NW> acc = lw_zero<NW>();
-                for (long long e4 = beg & ~3ll; e4 < end; e4 += 4) {
-                    acc = lw_or(acc, bu_gather4<NW>(a, e4, beg, end, scanned, fetched));
-                    if (lw_covers(acc, need)) break;
-                }
+                const LW<NW> acc = bu_scan_row<NW>(a, beg, end, need, scanned, fetched);
                 const LW<NW> found = lw_and(acc, need);
                 if (lw_any(found)) {
                     const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
@@ -412,11 +440,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_segment_kernel(Trav
         if (!lw_any(need)) continue;
         const long long beg = a.row_ptr[u] + (long long)k * a.seg;
         const long long end = min(beg + (long long)a.seg, a.row_ptr[u + 1]);
-        LW<NW> acc = lw_zero<NW>();
-        for (long long e4 = beg & ~3ll; e4 < end; e4 += 4) {
-            acc = lw_or(acc, bu_gather4<NW>(a, e4, beg, end, scanned, fetched));
-            if (lw_covers(acc, need)) break;
-        }
+        const LW<NW> acc = bu_scan_row<NW>(a, beg, end, need, scanned, fetched);
         const LW<NW> found = lw_and(acc, need);
         if (lw_any(found)) {
 #pragma unroll
