@@ -199,3 +199,36 @@ def test_full_size_config2_properties(pkg, ob, engine):
     o3 = (np.arange(len(pick) + 1) * s).astype(np.int64)
     want = ob.run(n, uv, o3, src.reshape(k, s)[pick].ravel())
     assert np.array_equal(base[pick], want.sums)
+
+
+def test_level_log_and_kernel_profiles(pkg, ob, expected, engine):
+    """The measurement side of the ABI: per-level records and per-kernel accounting add up."""
+    n, uv, offs, src = golden_case_inputs(pkg, ob, expected, "rmat16_64x4")
+    engine.set_graph_edges(n, uv)
+    engine.set_option("profile", 1)
+    try:
+        sums = engine.run(offs, src)
+    finally:
+        engine.set_option("profile", 0)
+    assert sums.tolist() == expected["rmat16_64x4"]["sums"]
+    st, log, prof = engine.stats(), engine.level_log(), engine.kernel_profiles()
+    assert log[0]["direction"] == 0 and log[0]["level"] == -1          # source injection record
+    assert len(log) == st["levels"] + st["batches"]                    # one record per level + injection
+    assert sum(r["scanned"] for r in log) == st["scanned_top_down"] + st["scanned_bottom_up"]
+    assert sum(p["scanned"] for p in prof) == sum(r["scanned"] for r in log)
+    assert sum(p["launches"] for p in prof) == st["kernel_launches"]
+    assert any(p["ms"] > 0 for p in prof) and st["alg_bytes"] > 0 and st["run_ms"] > 0
+
+
+def test_nccl_min_allreduce_two_gpus(pkg, tmp_path):
+    """msbfs_allreduce_min_u64 over a real ncclComm_t (needs two GPUs; skipped otherwise)."""
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    exe = str(tmp_path / "nccl_min_check")
+    src_file = os.path.join(os.path.dirname(__file__), "native", "nccl_min_check.cpp")
+    subprocess.run(["g++", "-std=c++17", "-O1", src_file, "-I", os.path.join(pkg.REPO_ROOT, "include"), "-L", pkg.PKG_DIR,
+                    "-lmsbfs", "-ldl", "-lpthread", f"-Wl,-rpath,{pkg.PKG_DIR}", "-o", exe], check=True)
+    res = subprocess.run([exe, "2"], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and ("OK:" in res.stdout or "SKIP:" in res.stdout), res.stdout + res.stderr  # NCCL prints a banner first
