@@ -52,7 +52,9 @@ int msbfs_destroy(msbfs_t* h);
 /* Tuning / test knobs; unknown keys -> MSBFS_ERR_INVALID.
  *   "lanes"      0 = auto (64/128/256 by group count), or 64 / 128 / 256
  *   "direction"  0 = direction-optimizing, 1 = top-down only, 2 = bottom-up only
- *   "alpha"      top-down is chosen while frontier_entries * alpha < unexplored_entries
+ *   "alpha"      cost of a top-down CSR entry relative to a bottom-up one (default 40): the next
+ *                level runs top-down while alpha * (frontier_entries + 0.8 frontier_vertices)
+ *                < unexplored_entries + alpha * unexplored_vertices
  *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off
  *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile) */
 int msbfs_set_option(msbfs_t* h, const char* key, int64_t value);

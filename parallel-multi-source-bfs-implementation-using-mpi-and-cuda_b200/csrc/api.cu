@@ -153,6 +153,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "deg_heavy")) {
         if (value < MSBFS_CHUNK || value > (1 << 30)) return msbfs_fail(MSBFS_ERR_INVALID, "deg_heavy out of range");
         h->opt_deg_heavy = (int)value;
+    } else if (!std::strcmp(key, "streak_max_deg")) {
+        if (value < 1 || value > 4096) return msbfs_fail(MSBFS_ERR_INVALID, "streak_max_deg out of range");
+        h->opt_streak_max_deg = (int)value;
     } else if (!std::strcmp(key, "streak_levels")) {
         if (value < 1) return msbfs_fail(MSBFS_ERR_INVALID, "streak_levels must be >= 1");
         h->opt_streak_levels = (int)std::min<int64_t>(value, 1 << 20);

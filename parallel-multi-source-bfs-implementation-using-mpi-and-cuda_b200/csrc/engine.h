@@ -69,6 +69,7 @@ struct LevelCtrl {
     unsigned long long active[MSBFS_MAX_NW];   /* lanes that carry a query group              */
     unsigned long long n_f, m_f;               /* new frontier: vertices, CSR entries         */
     long long          m_u;                    /* CSR entries of not-yet-full vertices        */
+    long long          n_u;                    /* not-yet-full vertices (degree > 0)          */
     unsigned long long scanned, words_fetched, examined, words_written; /* this level        */
     int level;                                 /* depth being expanded (-1 = injection)       */
     int log_pos;
@@ -165,9 +166,10 @@ struct msbfs_handle {
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
     int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
     int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
+    int opt_streak_max_deg = 256;              /* longest row for which the persistent kernel is used */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_seg = 256;                         /* bottom-up segment length (next graph load)      */
-    long long opt_alpha = 8;
+    long long opt_alpha = 40;
 
     /* stats of the last run */
     msbfs_stats stats{};

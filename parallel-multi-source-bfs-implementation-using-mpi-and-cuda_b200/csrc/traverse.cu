@@ -130,6 +130,22 @@ __device__ __forceinline__ ull warp_sum(ull v) {
     return v;
 }
 
+/* A vertex that has just been visited by every lane of the batch leaves the "unexplored"
+ * totals the direction heuristic works with: one vertex and deg CSR entries.  Both ride in
+ * one 64-bit accumulator (count << 40 | entries) until the warp flushes them. */
+constexpr int FULL_SHIFT = 40;
+__device__ __forceinline__ void note_full(ull& acc, long long deg) { acc += (1ull << FULL_SHIFT) + (ull)deg; }
+__device__ __forceinline__ void commit_full(LevelCtrl* c, ull packed) {
+    if (!packed) return;
+    atomicAdd((ull*)&c->m_u, (ull)(-(long long)(packed & ((1ull << FULL_SHIFT) - 1ull))));
+    atomicAdd((ull*)&c->n_u, (ull)(-(long long)(packed >> FULL_SHIFT)));
+}
+__device__ __forceinline__ ull warp_sum(ull v);
+__device__ __forceinline__ void flush_full(LevelCtrl* c, ull acc, int lane) {
+    acc = warp_sum(acc);
+    if (lane == 0) commit_full(c, acc);
+}
+
 __device__ __forceinline__ bool test_bit(const unsigned* bitmap, int v) {
     return (bitmap[v >> 5] >> (v & 31)) & 1u;
 }
@@ -273,7 +289,7 @@ template <int NW>
 __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) {
     const int lane = threadIdx.x & 31;
     const LW<NW> active = lw_from<NW>(a.ctrl->active);
-    long long mu_delta = 0;
+    ull full_acc = 0;
     for (int b = global_warp(); b < nblk; b += total_warps()) {
         const unsigned w = a.nxt_nz[b];
         if (w == 0u) continue;
@@ -287,14 +303,13 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
             lw_store<NW>(a.nxt, v, x);
             if (lw_covers(nv, active)) {
                 full_now = true;
-                mu_delta -= a.row_ptr[v + 1] - a.row_ptr[v];
+                note_full(full_acc, a.row_ptr[v + 1] - a.row_ptr[v]);
             }
         }
         const unsigned fb = __ballot_sync(0xffffffffu, full_now);
         if (fb && lane == 0) a.vis_full[b] |= fb;
     }
-    mu_delta = (long long)warp_sum((ull)mu_delta);
-    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+    flush_full(a.ctrl, full_acc, lane);
 }
 
 /* ------------------------------------------------------------ bottom-up --- */
@@ -373,7 +388,7 @@ template <int NW, int U>
 __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
-    long long mu_delta = 0;
+    ull full_acc = 0;
     for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
         const unsigned fullw = a.vis_full[b];
         if (fullw == 0xffffffffu) {
@@ -395,7 +410,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravA
                     lw_store<NW>(a.nxt, u, found);
                     ++written;
                     has_new = true;
-                    if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; mu_delta -= end - beg; }
+                    if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; note_full(full_acc, end - beg); }
                 }
             }
         }
@@ -404,8 +419,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravA
         bu_store_block_bits(a, b, lane, fullw, nz, fb);
     }
     flush_counters(a.ctrl, SLOT_BU_G2, scanned, fetched, examined, written);
-    mu_delta = (long long)warp_sum((ull)mu_delta);
-    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+    flush_full(a.ctrl, full_acc, lane);
 }
 
 /* Rows longer than a.seg entries: one thread per segment of a.seg entries, work items
@@ -458,7 +472,7 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
     const int lane = threadIdx.x & 31;
     const LW<NW> live = lw_from<NW>(a.ctrl->live);
     const LW<NW> active = lw_from<NW>(a.ctrl->active);
-    long long mu_delta = 0;
+    ull full_acc = 0;
     for (int b = global_warp(); b < nblk_hub; b += total_warps()) {
         const int u = (b << 5) + lane;
         const unsigned fullw = a.vis_full[b];
@@ -474,7 +488,7 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
                     lw_store<NW>(a.visited, u, nv);
                     lw_store<NW>(a.nxt, u, found);
                     has_new = true;
-                    if (lw_covers(nv, active)) { full_now = true; mu_delta -= a.row_ptr[u + 1] - a.row_ptr[u]; }
+                    if (lw_covers(nv, active)) { full_now = true; note_full(full_acc, a.row_ptr[u + 1] - a.row_ptr[u]); }
                 }
             }
         }
@@ -485,8 +499,7 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
             if (fb) a.vis_full[b] = fullw | fb;
         }
     }
-    mu_delta = (long long)warp_sum((ull)mu_delta);
-    if (lane == 0 && mu_delta) atomicAdd((ull*)&a.ctrl->m_u, (ull)mu_delta);
+    flush_full(a.ctrl, full_acc, lane);
 }
 
 /* ------------------------------------------- per-lane counts (popcount) --- */
@@ -626,7 +639,7 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
 
 /* ------------------------------------------------------ level bookkeeping --- */
 
-__global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz) {
+__global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long long n_active) {
     const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
     c->cnt[j] = 0ull;
     c->sums[j] = 0ull;
@@ -639,7 +652,7 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz) {
         c->active[j] = m;
     }
     if (j == 0) {
-        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->heavy_frontier = 0u;
+        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->n_u = n_active; c->heavy_frontier = 0u;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level = -1;
     }
@@ -660,8 +673,14 @@ __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int l
     if (j == 0) {
         const ull nf = c->n_f, mf = c->m_f;
         const long long mu = c->m_u;
-        int next = (force_direction == 1 || force_direction == 2) ? force_direction
-                   : (((long long)mf * alpha < mu) ? 1 : 2);
+        /* Top-down costs about alpha x more per CSR entry than bottom-up (random visited read
+         * + atomic OR vs a streamed col entry and a bitmap probe); both pay per vertex they
+         * touch: the frontier's vertices top-down, every not-yet-full vertex bottom-up.
+         * Fitted on Kronecker-26, ER-24 and the 4096^2 lattice. */
+        const long long nu = c->n_u;
+        const long long td_cost = alpha * (long long)mf + (alpha * 4 / 5) * (long long)nf;
+        const long long bu_cost = mu + alpha * nu;
+        int next = (force_direction == 1 || force_direction == 2) ? force_direction : ((td_cost < bu_cost) ? 1 : 2);
         if (c->log_pos < log_cap) {
             LevelLog& l = log[c->log_pos];
             l.level = c->level; l.direction = direction;
@@ -696,10 +715,9 @@ __global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelV
  * cooperative kernel keeps one grid resident and runs consecutive top-down levels —
  * expand, finalize + per-lane count, epilogue — separated by grid-wide barriers, until
  * the BFS is done or the direction heuristic asks for a bottom-up level.  Used only when
- * every row is short (max degree <= STREAK_MAX_DEG), so a frontier vertex is one thread.
+ * every row is short (max degree <= option "streak_max_deg", default 32), so a frontier vertex is one thread.
  * On return the host finds ctrl / verdict exactly as after a normal epilogue, plus the
  * number of levels run (the frontier buffers have swapped that many times). */
-constexpr int STREAK_MAX_DEG = 32;
 
 /* A warp takes a tile of 32 bitmap words (1024 vertices, one coalesced 128-byte read) and
  * hands the set bits out densely: round r gives lane j the (32 r + j)-th set bit of the
@@ -743,7 +761,7 @@ __global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog*
     cg::grid_group grid = cg::this_grid();
     __shared__ unsigned s_cnt[64 * NW];
     __shared__ ull s_ctr[6]; /* scanned, fetched, examined, written, nf, mf */
-    __shared__ long long s_mu;
+    __shared__ ull s_mu; /* packed newly-full totals, see note_full */
     __shared__ unsigned s_flags; /* bit 0: this block saw new frontier words */
     const int lane = threadIdx.x & 31;
     const int nblk = a.n_pad >> 5;
@@ -794,7 +812,7 @@ __global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog*
          *      lanes), which keeps the kernel at 64 registers. */
         {
             ull nf = 0, mf = 0;
-            long long mu_delta = 0;
+            ull full_acc = 0;
             bool warp_any = false;
             const LW<NW> active = lw_from<NW>(a.ctrl->active);
             for (int t = global_warp(); t < ntiles; t += total_warps()) {
@@ -840,7 +858,7 @@ __global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog*
                         ++nf;
                         mf += (ull)deg[q];
                         if (lw_covers(nv, active)) {
-                            mu_delta -= deg[q];
+                            note_full(full_acc, deg[q]);
                             atomicOr(&a.vis_full[v[q] >> 5], 1u << (v[q] & 31));
                         }
                     }
@@ -848,10 +866,10 @@ __global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog*
             }
             if (warp_any) {
                 nf = warp_sum(nf); mf = warp_sum(mf);
-                mu_delta = (long long)warp_sum((ull)mu_delta);
+                full_acc = warp_sum(full_acc);
                 if (lane == 0) {
                     atomicAdd(&s_ctr[4], nf); atomicAdd(&s_ctr[5], mf);
-                    if (mu_delta) atomicAdd((ull*)&s_mu, (ull)mu_delta);
+                    if (full_acc) atomicAdd(&s_mu, full_acc);
                     atomicOr(&s_flags, 1u);
                 }
             }
@@ -866,7 +884,7 @@ __global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog*
             if (s_ctr[2]) { atomicAdd(&a.ctrl->examined, s_ctr[2]); atomicAdd(&a.ctrl->k_examined[SLOT_TD_G2], s_ctr[2]); }
             if (s_ctr[3]) { atomicAdd(&a.ctrl->words_written, s_ctr[3]); atomicAdd(&a.ctrl->k_written[SLOT_TD_G2], s_ctr[3]); }
             if (s_ctr[4]) { atomicAdd(&a.ctrl->n_f, s_ctr[4]); atomicAdd(&a.ctrl->m_f, s_ctr[5]); }
-            if (s_mu) atomicAdd((ull*)&a.ctrl->m_u, (ull)s_mu);
+            commit_full(a.ctrl, s_mu);
         }
         __threadfence();
         grid.sync();
@@ -964,7 +982,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
     /* persistent top-down kernel: only when every row is short and the device can co-schedule the grid */
     int streak_grid = 0;
-    if (h->opt_streak && h->max_degree <= (unsigned)STREAK_MAX_DEG) {
+    if (h->opt_streak && h->max_degree <= (unsigned)h->opt_streak_max_deg) {
         int coop = 0, per_sm = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device);
         if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, td_streak_kernel<NW>, CTA, 0) == cudaSuccess && per_sm > 0)
@@ -983,7 +1001,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
     for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
         const int lanes = std::min(lanes_per_batch, K - group_base);
-        L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz); });
+        L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz, (long long)h->n_active); });
         MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
         MSBFS_CUDA(cudaMemsetAsync(h->d_bitmaps, 0, sizeof(unsigned) * 3 * (size_t)nblk, s));
         a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk;
