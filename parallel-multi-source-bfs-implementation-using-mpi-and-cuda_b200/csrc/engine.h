@@ -162,6 +162,10 @@ struct msbfs_handle {
     size_t h_pinned_io_bytes = 0;
     unsigned long long* d_scalar = nullptr; /* 8-byte scratch for the packed min all-reduce */
 
+    /* pinned staging buffers of the loader (api.cu), allocated on first use */
+    char* stage_buf[8] = {};
+    cudaEvent_t stage_ev[8] = {};
+
     /* options */
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
     int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
