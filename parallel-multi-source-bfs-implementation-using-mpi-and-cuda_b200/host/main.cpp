@@ -114,14 +114,27 @@ int main(int argc, char* argv[]) {
     if (mine > 0 && msbfs_run(eng, mine, q_offsets + first, q_sources, local_F.data()) != MSBFS_OK)
         die(world_rank, "msbfs_run");
 
-    uint64_t packed = UINT64_MAX;
-    if (msbfs_argmin_packed(local_F.data(), first, mine, &packed) != MSBFS_OK) die(world_rank, "argmin");
-    unsigned long long best = packed;
-    MPI_Allreduce(MPI_IN_PLACE, &best, 1, MPI_UNSIGNED_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
-
+    /* one 8-byte min all-reduce of (F << 24 | id); when a sum or an id does not fit the packed
+     * word (F >= 2^39 or K > 2^24) fall back to two reductions: min F, then min id among its holders */
     int32_t minK = -1;
     int64_t minF = -1; /* K = 0 keeps (-1, -1), main.cu:379-380 */
-    msbfs_unpack_argmin((uint64_t)best, &minK, &minF);
+    uint64_t packed = UINT64_MAX;
+    int packable = msbfs_argmin_packed(local_F.data(), first, mine, &packed) == MSBFS_OK ? 1 : 0;
+    MPI_Allreduce(MPI_IN_PLACE, &packable, 1, MPI_INT, MPI_MIN, MPI_COMM_WORLD);
+    if (packable) {
+        unsigned long long best = packed;
+        MPI_Allreduce(MPI_IN_PLACE, &best, 1, MPI_UNSIGNED_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
+        msbfs_unpack_argmin((uint64_t)best, &minK, &minF);
+    } else {
+        int32_t lk = -1;
+        int64_t lf = -1;
+        msbfs_argmin(mine, local_F.data(), &lk, &lf);
+        long long gf = lk >= 0 ? lf : INT64_MAX;
+        MPI_Allreduce(MPI_IN_PLACE, &gf, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
+        long long gk = (lk >= 0 && lf == gf) ? (long long)first + lk : INT64_MAX;
+        MPI_Allreduce(MPI_IN_PLACE, &gk, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
+        if (gk != INT64_MAX) { minK = (int32_t)gk; minF = gf; }
+    }
 
     auto end_computation = chrono::high_resolution_clock::now();
     double computation_time = chrono::duration<double>(end_computation - start_computation).count();

@@ -16,6 +16,7 @@
 #include <string.h>
 #include <sys/mman.h>
 #include <sys/wait.h>
+#include <time.h>
 #include <unistd.h>
 
 #define MINIMPI_HDR_BYTES 16384
@@ -93,17 +94,33 @@ int main(int argc, char** argv) {
         g_pids[r] = pid;
     }
 
+    /* Like a real mpirun, a rank that exits non-zero ends the job with that status.  The
+     * peers get a short grace period first: when every rank is leaving on its own (the usage
+     * path: all return -1, rank 0 prints) nobody must be cut off mid-message; ranks that are
+     * stuck in a collective waiting for the dead rank are terminated after it. */
     int rc = 0, alive = np;
+    double deadline = 0.0;
     while (alive > 0) {
         int status = 0;
-        pid_t pid = wait(&status);
+        pid_t pid = waitpid(-1, &status, rc ? WNOHANG : 0);
         if (pid < 0) { if (errno == EINTR) continue; break; }
+        if (pid == 0) { /* after a failure: poll until the grace period is over */
+            struct timespec ts;
+            clock_gettime(CLOCK_MONOTONIC, &ts);
+            const double now = (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+            if (now >= deadline) { kill_all(SIGTERM); deadline = now + 3600.0; }
+            struct timespec nap = {0, 2000000};
+            nanosleep(&nap, NULL);
+            continue;
+        }
         for (int r = 0; r < np; ++r) if (g_pids[r] == pid) g_pids[r] = 0;
         --alive;
         int code = WIFEXITED(status) ? WEXITSTATUS(status) : 128 + WTERMSIG(status);
         if (code != 0 && rc == 0) {
             rc = code;
-            kill_all(SIGTERM);
+            struct timespec ts;
+            clock_gettime(CLOCK_MONOTONIC, &ts);
+            deadline = (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec + 0.5;
         }
     }
     shm_unlink(g_shm);

@@ -34,10 +34,36 @@ def allreduce_packed_min(packed: int, device=None) -> int:
     return UINT64_MAX if v == (1 << 63) - 1 else v
 
 
+def _allreduce_min_i64(value: int, device=None) -> int:
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return value
+    t = torch.tensor([value], dtype=torch.int64, device=device if device is not None else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return int(t.item())
+
+
 def distributed_argmin(local_sums: np.ndarray, first_qid: int, device=None):
-    """(min_k, min_f) over all ranks' groups; (-1, -1) when there are none (K = 0)."""
-    packed = argmin_packed(np.asarray(local_sums, dtype=np.int64), first_qid)
-    return unpack_argmin(allreduce_packed_min(packed, device))
+    """(min_k, min_f) over all ranks' groups; (-1, -1) when there are none (K = 0).
+    One packed 8-byte reduction; if a sum or an id does not fit the packed word on any rank
+    (F >= 2^39 or id >= 2^24), two plain reductions instead: min F, then the smallest id
+    among its holders — the same lowest-index tie-break (main.cu:391-395)."""
+    from . import MsbfsError, argmin
+
+    local_sums = np.asarray(local_sums, dtype=np.int64)
+    try:
+        packed, ok = argmin_packed(local_sums, first_qid), 1
+    except MsbfsError:
+        packed, ok = UINT64_MAX, 0
+    if _allreduce_min_i64(ok, device) == 1:
+        return unpack_argmin(allreduce_packed_min(packed, device))
+    big = (1 << 63) - 1
+    lk, lf = argmin(local_sums)
+    gf = _allreduce_min_i64(lf if lk >= 0 else big, device)
+    gk = _allreduce_min_i64(first_qid + lk if (lk >= 0 and lf == gf) else big, device)
+    return (-1, -1) if gk == big else (gk, gf)
 
 
 __all__ = ["shard_range", "allreduce_packed_min", "distributed_argmin", "UINT64_MAX"]

@@ -35,7 +35,7 @@ def _worker(rank, world, port, sums, lanes, out_path):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,case", [(2, "ties"), (2, "empty"), (3, "random"), (2, "single_batch")])
+@pytest.mark.parametrize("world,case", [(2, "ties"), (2, "empty"), (3, "random"), (2, "single_batch"), (3, "too_big_to_pack")])
 def test_distributed_argmin(pkg, ob, tmp_path, world, case):
     rng = np.random.default_rng(5)
     lanes = 4  # small batches so that several ranks own groups
@@ -43,6 +43,8 @@ def test_distributed_argmin(pkg, ob, tmp_path, world, case):
         sums = [9, 7, 8, 7, 7, 30, 7, 12, 7]
     elif case == "empty":
         sums = []
+    elif case == "too_big_to_pack":
+        sums = [(1 << 45) + 5, 1 << 41, (1 << 45) + 5, 1 << 41, 1 << 50, 7 << 40, 1 << 41, 9 << 40, 1 << 42]  # F >= 2^39
     elif case == "single_batch":
         sums = [5, 3, 3]  # one batch: rank 1 owns nothing and contributes UINT64_MAX
     else:
