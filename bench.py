@@ -238,7 +238,7 @@ def run_reference_arm(args, wl, rank):
     line = {
         "impl": "reference", "metric": "GTEPS", "value": v, "unit": "GTEPS", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": statistics.median(step_s) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "int32 distances / int64 sums", "data": "synthetic",
+        "dtype": "int64", "data": "synthetic",
         "config": {"workload": args.workload, "description": wl["desc"], "graph_seed": GRAPH_SEED, "query_seed": QUERY_SEED},
         "queries_per_sec": statistics.median(qps),
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": cores_used, "kind": kind_s, "sample": sample_desc},
@@ -466,7 +466,7 @@ def run_ours(args, wl, rank, local_rank, world):
     line = {
         "metric": "GTEPS", "value": value, "unit": "GTEPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "u64 lane masks / int64 sums", "data": "synthetic",
+        "dtype": "u64", "data": "synthetic",
         "config": {"workload": args.workload, "description": wl["desc"], "graph_seed": GRAPH_SEED, "query_seed": QUERY_SEED,
                    "lanes": stats.get("lanes"), "batches_rank0": stats.get("batches"), "levels_rank0": stats.get("levels"),
                    "levels_top_down": stats.get("levels_top_down"), "levels_bottom_up": stats.get("levels_bottom_up"),
