@@ -6,7 +6,7 @@
 A step = one pass of the hot path over the whole query set of the workload: every group's
 BFS + distance sum (what the reference does in its "Computation time" window,
 /root/reference/main.cu:301-399).  With N > 1 (one process per GPU, torchrun) the groups
-are sharded in contiguous 256-lane batches over the ranks (strong scaling: total work
+are sharded in contiguous 512-lane batches over the ranks (strong scaling: total work
 fixed), the graph is replicated (each rank generates it on its own GPU), and the only
 exchange is one 8-byte packed min all-reduce per step.
 

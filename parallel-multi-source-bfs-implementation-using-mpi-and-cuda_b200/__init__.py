@@ -223,14 +223,20 @@ def unpack_argmin(packed: int):
     return k.value, f.value
 
 
-def shard_range(num_groups: int, rank: int, world: int, lanes: int = 256):
-    """Contiguous block of whole lane batches owned by `rank` (replaces the round-robin
-    `kidx = rank; kidx += world_size` of main.cu:305).  Any partition gives the same
-    argmin; whole batches keep every GPU's lane words full."""
+def shard_range(num_groups: int, rank: int, world: int, lanes: int = 512):
+    """Contiguous block of groups owned by `rank` (replaces the round-robin
+    `kidx = rank; kidx += world_size` of main.cu:305).  Any partition gives the same argmin.
+    Whole `lanes`-wide batches per rank keep every GPU's lane words full; when there are
+    fewer batches than ranks the groups are split evenly in multiples of 64 lanes instead,
+    so that no GPU idles."""
     batches = (num_groups + lanes - 1) // lanes
-    b0 = (batches * rank) // world
-    b1 = (batches * (rank + 1)) // world
-    return min(b0 * lanes, num_groups), min(b1 * lanes, num_groups)
+    if batches >= world:
+        b0 = (batches * rank) // world
+        b1 = (batches * (rank + 1)) // world
+        return min(b0 * lanes, num_groups), min(b1 * lanes, num_groups)
+    per = ((num_groups + world - 1) // world + 63) // 64 * 64
+    lo = min(rank * per, num_groups)
+    return lo, min(lo + per, num_groups)
 
 
 # --------------------------------------------------------------------------- engine

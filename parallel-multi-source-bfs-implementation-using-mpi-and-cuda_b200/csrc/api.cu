@@ -154,8 +154,8 @@ extern "C" int msbfs_destroy(msbfs_t* h) {
 extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     if (!h || !key) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_option: null argument");
     if (!std::strcmp(key, "lanes")) {
-        if (value != 0 && value != 64 && value != 128 && value != 256)
-            return msbfs_fail(MSBFS_ERR_INVALID, "lanes must be 0, 64, 128 or 256");
+        if (value != 0 && value != 64 && value != 128 && value != 256 && value != 512)
+            return msbfs_fail(MSBFS_ERR_INVALID, "lanes must be 0, 64, 128, 256 or 512");
         h->opt_lanes = (int)value;
     } else if (!std::strcmp(key, "direction")) {
         if (value < 0 || value > 2) return msbfs_fail(MSBFS_ERR_INVALID, "direction must be 0, 1 or 2");

@@ -34,7 +34,7 @@
 #include <cstdint>
 #include <vector>
 
-constexpr int MSBFS_MAX_NW      = 4;     /* 256 lanes */
+constexpr int MSBFS_MAX_NW      = 8;     /* 512 lanes (experimental; 256 is the default ceiling) */
 constexpr int MSBFS_MAX_LANES   = 64 * MSBFS_MAX_NW;
 constexpr int MSBFS_CHUNK       = 1024;  /* CSR entries per heavy-row chunk (one warp) */
 constexpr int MSBFS_DEG_HEAVY   = 1024;  /* deg >= this: row is split into chunks      */

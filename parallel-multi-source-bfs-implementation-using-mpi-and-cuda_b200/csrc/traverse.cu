@@ -385,7 +385,7 @@ __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, in
  * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
  * each thread leaves its loop as soon as its own need is covered. */
 template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? 2 : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     ull full_acc = 0;
@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_thread_kernel(TravA
  * Segments of a row co-operate through hub_acc: a segment first subtracts what earlier
  * segments already found and skips the row when nothing is left to find. */
 template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : 4) bu_segment_kernel(TravArgs a) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? 2 : 4) bu_segment_kernel(TravArgs a) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
@@ -663,14 +663,16 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long l
  * `direction` is what the level just finished used (0 = injection). */
 __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
                                               int direction, long long alpha, int force_direction) {
-    const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
-    const ull cnt = c->cnt[j];
-    c->sums[j] += (ull)(c->level + 1) * cnt;
-    c->cnt[j] = 0ull;
-    const unsigned bal = __ballot_sync(0xffffffffu, cnt != 0ull);
-    if ((j & 31) == 0) reinterpret_cast<unsigned*>(c->live)[j >> 5] = bal;
+    /* any block size that is a multiple of 32 */
+    for (int j = threadIdx.x; j < MSBFS_MAX_LANES; j += blockDim.x) {
+        const ull cnt = c->cnt[j];
+        c->sums[j] += (ull)(c->level + 1) * cnt;
+        c->cnt[j] = 0ull;
+        const unsigned bal = __ballot_sync(0xffffffffu, cnt != 0ull);
+        if ((j & 31) == 0) reinterpret_cast<unsigned*>(c->live)[j >> 5] = bal;
+    }
     __syncthreads();
-    if (j == 0) {
+    if (threadIdx.x == 0) {
         const ull nf = c->n_f, mf = c->m_f;
         const long long mu = c->m_u;
         /* Top-down costs about alpha x more per CSR entry than bottom-up (random visited read
@@ -756,7 +758,7 @@ struct TileBits {
 };
 
 template <int NW>
-__global__ void __launch_bounds__(CTA, 4) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
+__global__ void __launch_bounds__(CTA, (NW == 8) ? 2 : 4) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
                                                            long long alpha, int force_direction, int max_levels) {
     cg::grid_group grid = cg::this_grid();
     __shared__ unsigned s_cnt[64 * NW];
@@ -1162,9 +1164,11 @@ int pick_nw(const msbfs_handle* h) {
     if (h->opt_lanes == 64) return 1;
     if (h->opt_lanes == 128) return 2;
     if (h->opt_lanes == 256) return 4;
+    if (h->opt_lanes == 512) return 8;
     if (h->q_groups <= 64) return 1;
     if (h->q_groups <= 128) return 2;
-    return 4;
+    if (h->q_groups <= 256) return 4;
+    return 8; /* 512 lanes: one 64-byte word per vertex (two sectors per gather) */
 }
 
 int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_out) {
@@ -1201,6 +1205,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     MSBFS_CUDA(cudaEventRecord(ev0, s));
     if (nw == 1) rc = run_batches<1>(h, want_reached, reached_out);
     else if (nw == 2) rc = run_batches<2>(h, want_reached, reached_out);
+    else if (nw == 8) rc = run_batches<8>(h, want_reached, reached_out);
     else rc = run_batches<4>(h, want_reached, reached_out);
     if (rc) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return rc; }
     MSBFS_CUDA(cudaEventRecord(ev1, s));

@@ -10,7 +10,7 @@
  *   - every rank loads the graph itself through the pinned/async loader and builds
  *     the CSR on its GPU (no host CSR, no MPI_Bcast of up to 8 GiB, main.cu:237-255);
  *   - queries are read by every rank (a few KB; replaces 2K broadcasts, main.cu:264-280);
- *   - ranks take contiguous blocks of whole lane batches instead of round-robin
+ *   - ranks take contiguous blocks of whole lane batches (512 groups) instead of round-robin
  *     single queries (main.cu:303-307);
  *   - the (q, F) Pair gather + scatter + two-pass argmin (main.cu:324-397) becomes one
  *     8-byte unsigned-min all-reduce of (F << 24 | q).
@@ -103,11 +103,20 @@ int main(int argc, char* argv[]) {
     /* ---- computation window (main.cu:301 -> 399) ---------------------------- */
     auto start_computation = chrono::high_resolution_clock::now();
 
-    /* contiguous blocks of whole 256-lane batches per rank */
-    const int lanes = 256;
+    /* contiguous shares: whole 512-lane batches per rank, or — with fewer batches than ranks —
+     * an even split in multiples of 64 lanes so that no GPU idles */
+    const int lanes = 512;
     const int64_t batches = ((int64_t)K + lanes - 1) / lanes;
-    const int64_t b0 = batches * world_rank / world_size, b1 = batches * (world_rank + 1) / world_size;
-    const int32_t first = (int32_t)min<int64_t>(b0 * lanes, K), last = (int32_t)min<int64_t>(b1 * lanes, K);
+    int32_t first, last;
+    if (batches >= world_size) {
+        const int64_t b0 = batches * world_rank / world_size, b1 = batches * (world_rank + 1) / world_size;
+        first = (int32_t)min<int64_t>(b0 * lanes, K);
+        last = (int32_t)min<int64_t>(b1 * lanes, K);
+    } else {
+        const int64_t per = (((int64_t)K + world_size - 1) / world_size + 63) / 64 * 64;
+        first = (int32_t)min<int64_t>(per * world_rank, K);
+        last = (int32_t)min<int64_t>((int64_t)first + per, K);
+    }
     const int32_t mine = last - first;
 
     vector<int64_t> local_F((size_t)max(mine, 1), 0);

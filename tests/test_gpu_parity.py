@@ -32,7 +32,7 @@ def test_golden_all_modes(pkg, ob, expected, engine, name):
     case = expected[name]
     engine.set_graph_edges(n, uv)
     try:
-        for lanes in (0, 64, 128, 256):
+        for lanes in (0, 64, 128, 256, 512):
             for direction in (0, 1, 2):
                 engine.set_option("lanes", lanes)
                 engine.set_option("direction", direction)
