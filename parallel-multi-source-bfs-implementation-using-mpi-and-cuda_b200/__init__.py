@@ -20,7 +20,7 @@ import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(PKG_DIR)
-LIB_PATH = os.path.join(PKG_DIR, "libmsbfs.so")
+LIB_PATH = os.environ.get("MSBFS_LIB", os.path.join(PKG_DIR, "libmsbfs.so"))  # override: A/B builds of the kernels
 HEADER_PATH = os.path.join(REPO_ROOT, "include", "msbfs.h")
 
 GEN_RMAT, GEN_KRON, GEN_LATTICE, GEN_ER = 0, 1, 2, 3

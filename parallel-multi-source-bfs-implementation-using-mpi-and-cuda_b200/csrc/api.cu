@@ -183,7 +183,7 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "streak")) {
         h->opt_streak = value != 0;
     } else if (!std::strcmp(key, "seg")) {
-        if (value < 8 || value > (1 << 20)) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
+        if (value != 0 && (value < 8 || value > (1 << 20))) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
         h->opt_seg = (int)value;
     } else if (!std::strcmp(key, "profile")) {
         h->opt_profile = value != 0;

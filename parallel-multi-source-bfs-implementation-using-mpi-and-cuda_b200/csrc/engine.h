@@ -172,7 +172,7 @@ struct msbfs_handle {
     int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
     int opt_streak_max_deg = 256;              /* longest row for which the persistent kernel is used */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
-    int opt_seg = 256;                         /* bottom-up segment length (next graph load)      */
+    int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     long long opt_alpha = 40;
 
     /* stats of the last run */

@@ -258,7 +258,9 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
 
     /* bottom-up segments of the long rows (deg > seg), level-major */
     {
-        const int seg = h->opt_seg;
+        /* segment length: 256 entries on small graphs (more segments = more threads), up to 1024 on
+         * multi-billion-entry ones (fewer atomics and look-ups); measured in profiles/r1/sweep_r2a/b.txt */
+        const int seg = h->opt_seg > 0 ? h->opt_seg : (int)std::min<long long>(1024, std::max<long long>(256, nnz >> 21));
         DevBuf lim, out;
         const unsigned limit = (unsigned)seg;
         int first_short = 0;

@@ -47,6 +47,9 @@ namespace {
 typedef unsigned long long ull;
 
 constexpr int CTA = 256;
+#ifndef MSBFS_NW8_BLOCKS
+#define MSBFS_NW8_BLOCKS 2 /* resident 256-thread blocks per SM asked of the 512-lane bottom-up kernels */
+#endif
 
 /* ------------------------------------------------------------ lane words --- */
 
@@ -385,7 +388,7 @@ __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, in
  * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
  * each thread leaves its loop as soon as its own need is covered. */
 template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? 2 : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     ull full_acc = 0;
@@ -429,7 +432,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? 2 : 4) bu_thr
  * Segments of a row co-operate through hub_acc: a segment first subtracts what earlier
  * segments already found and skips the row when nothing is left to find. */
 template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? 2 : 4) bu_segment_kernel(TravArgs a) {
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
