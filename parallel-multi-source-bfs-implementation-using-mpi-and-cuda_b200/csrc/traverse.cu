@@ -565,6 +565,30 @@ template <int NC> struct Csa {
             }
         }
     }
+    /* four words at once: two full adders into slice 0, one into slice 1, then a single
+     * carry ripples from slice 2 — 12 logic ops per 32 lanes x 4 words */
+    __device__ __forceinline__ void add4(const ull* w0, const ull* w1, const ull* w2, const ull* w3) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const int sh = (c & 1) * 32;
+            const unsigned x0 = (unsigned)(w0[c >> 1] >> sh), x1 = (unsigned)(w1[c >> 1] >> sh);
+            const unsigned x2 = (unsigned)(w2[c >> 1] >> sh), x3 = (unsigned)(w3[c >> 1] >> sh);
+            const unsigned t1 = x0 ^ x1 ^ x2;
+            const unsigned c1 = (x0 & x1) | (x0 & x2) | (x1 & x2);
+            const unsigned s0 = sl[0][c];
+            sl[0][c] = s0 ^ t1 ^ x3;
+            const unsigned c2 = (s0 & t1) | (s0 & x3) | (t1 & x3);
+            const unsigned s1 = sl[1][c];
+            sl[1][c] = s1 ^ c1 ^ c2;
+            unsigned carry = (s1 & c1) | (s1 & c2) | (c1 & c2);
+#pragma unroll
+            for (int s = 2; s < K; ++s) {
+                const unsigned t = sl[s][c] & carry;
+                sl[s][c] ^= carry;
+                carry = t;
+            }
+        }
+    }
     /* warp-collective */
     __device__ __forceinline__ void flush(int lane) {
 #pragma unroll
@@ -582,54 +606,81 @@ template <int NC> struct Csa {
  *         frontier's vertex and entry totals for the direction heuristic;
  * mode 1: count visited words of vertices whose degree has bit `degbit` set into
  *         out[] scaled by 2^degbit (reached CSR entries per lane, for TEPS). */
+/* A lane word wider than 256 bits is counted in 256-bit parts by different warps (a warp
+ * keeps the bit-sliced counters of one part in registers), four vertices' words per pass. */
+template <int NW> struct CountShape {
+    static constexpr int PARTS = (NW > 4) ? NW / 4 : 1;  /* 256-bit parts per lane word */
+    static constexpr int PW = NW / PARTS;                 /* 64-bit words per part        */
+};
+template <int PW> struct alignas(8 * PW) PartWord { ull w[PW]; };
+
 template <int NW, int MODE>
 __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int degbit, ull* __restrict__ out) {
-    constexpr int NC = 2 * NW;
+    constexpr int PARTS = CountShape<NW>::PARTS, PW = CountShape<NW>::PW, NC = 2 * PW;
+    typedef PartWord<PW> Part;
     __shared__ unsigned s_cnt[64 * NW];
     for (int i = threadIdx.x; i < 64 * NW; i += CTA) s_cnt[i] = 0u;
     __syncthreads();
     const int lane = threadIdx.x & 31;
+    const int part = global_warp() % PARTS;          /* this warp's slice of every word */
+    const int wslot = global_warp() / PARTS, nslots = total_warps() / PARTS;
+    const ull* words = (MODE == 0) ? a.nxt : a.visited;
     Csa<NC> csa;
     csa.init();
     int pending = 0;
     ull nf = 0, mf = 0;
     unsigned heavy = 0u;
-    /* two blocks per pass: both bitmap words, then both lane words, are in flight together */
-    for (int b0 = 2 * global_warp(); b0 < nblk; b0 += 2 * total_warps()) {
-        const int b1 = b0 + 1;
-        const bool has1 = b1 < nblk;
-        if (MODE == 0) {
-            const unsigned w0 = a.nxt_nz[b0], w1 = has1 ? a.nxt_nz[b1] : 0u;
-            if ((w0 | w1) == 0u) continue;
-            if ((w0 && b0 < a.blk_heavy) || (w1 && b1 < a.blk_heavy)) heavy = 1u;
-            const bool on0 = (w0 >> lane) & 1u, on1 = (w1 >> lane) & 1u;
-            const int v0 = (b0 << 5) + lane, v1 = (b1 << 5) + lane;
-            LW<NW> x0 = lw_zero<NW>(), x1 = lw_zero<NW>();
-            if (on0) x0 = lw_load<NW>(a.nxt, v0);
-            if (on1) x1 = lw_load<NW>(a.nxt, v1);
-            csa.add2(x0.w, x1.w); /* a word that is off is zero and adds nothing */
-            if (on0) { ++nf; mf += (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]); }
-            if (on1) { ++nf; mf += (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]); }
-        } else {
-            const int v0 = (b0 << 5) + lane, v1 = (b1 << 5) + lane;
-            const ull d0 = (ull)(a.row_ptr[v0 + 1] - a.row_ptr[v0]);
-            const ull d1 = has1 ? (ull)(a.row_ptr[v1 + 1] - a.row_ptr[v1]) : 0ull;
-            if ((d0 >> degbit) & 1ull) { const LW<NW> x = lw_load<NW>(a.visited, v0); csa.add(x.w); }
-            if ((d1 >> degbit) & 1ull) { const LW<NW> x = lw_load<NW>(a.visited, v1); csa.add(x.w); }
+    Part zero;
+#pragma unroll
+    for (int i = 0; i < PW; ++i) zero.w[i] = 0ull;
+    if (wslot < nslots) {
+        for (int b0 = 4 * wslot; b0 < nblk; b0 += 4 * nslots) {
+            bool on[4];
+            int v[4];
+            unsigned any = 0u;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int b = b0 + q;
+                v[q] = (b << 5) + lane;
+                on[q] = false;
+                if (b < nblk) {
+                    if (MODE == 0) {
+                        const unsigned w = a.nxt_nz[b];
+                        any |= w;
+                        on[q] = (w >> lane) & 1u;
+                        if (w && b < a.blk_heavy) heavy = 1u;
+                    } else {
+                        const ull d = (ull)(a.row_ptr[v[q] + 1] - a.row_ptr[v[q]]);
+                        on[q] = (d >> degbit) & 1ull;
+                        any |= on[q];
+                    }
+                }
+            }
+            if (MODE == 0 && any == 0u) continue; /* warp-uniform: the bitmap words are */
+            Part x[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                x[q] = on[q] ? *reinterpret_cast<const Part*>(words + (long long)v[q] * NW + part * PW) : zero;
+            csa.add4(x[0].w, x[1].w, x[2].w, x[3].w); /* a word that is off is zero and adds nothing */
+            if (MODE == 0 && part == 0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (on[q]) { ++nf; mf += (ull)(a.row_ptr[v[q] + 1] - a.row_ptr[v[q]]); }
+            }
+            pending += 4;
+            if (pending >= 28) { csa.flush(lane); pending = 0; }
         }
-        pending += 2;
-        if (pending >= 30) { csa.flush(lane); pending = 0; }
     }
     csa.flush(lane);
 #pragma unroll
     for (int c = 0; c < NC; ++c)
-        if (csa.cnt[c]) atomicAdd(&s_cnt[c * 32 + lane], csa.cnt[c]);
+        if (csa.cnt[c]) atomicAdd(&s_cnt[part * 64 * PW + c * 32 + lane], csa.cnt[c]);
     __syncthreads();
     for (int i = threadIdx.x; i < 64 * NW; i += CTA) {
-        const unsigned v = s_cnt[i];
-        if (v) {
-            if (MODE == 0) atomicAdd(&a.ctrl->cnt[i], (ull)v);
-            else atomicAdd(&out[i], (ull)v << degbit);
+        const unsigned cv = s_cnt[i];
+        if (cv) {
+            if (MODE == 0) atomicAdd(&a.ctrl->cnt[i], (ull)cv);
+            else atomicAdd(&out[i], (ull)cv << degbit);
         }
     }
     if (MODE == 0) {
