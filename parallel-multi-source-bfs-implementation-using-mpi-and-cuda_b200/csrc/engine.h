@@ -191,5 +191,6 @@ void msbfs_release_graph(msbfs_handle* h);
 int msbfs_traverse(msbfs_handle* h);
 int msbfs_reached_entries_impl(msbfs_handle* h, int64_t* out_entries, int32_t count);
 void msbfs_release_traversal(msbfs_handle* h);
+void msbfs_prealloc_traversal(msbfs_handle* h);
 
 #endif

@@ -335,5 +335,6 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
     h->n_active = n_active; h->n_pad = n_pad;
     h->has_graph = true;
     h->build_ms = ms;
+    msbfs_prealloc_traversal(h);
     return MSBFS_OK;
 }

@@ -1168,8 +1168,10 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     return MSBFS_OK;
 }
 
+/* Buffers are sized for `nw` 64-bit words per lane word and serve any narrower width too
+ * (every kernel strides by its own NW; acc / hub_acc are all-zero whatever the width). */
 int ensure_traversal_buffers(msbfs_handle* h, int nw) {
-    if (h->nw_alloc == nw && h->d_visited) return MSBFS_OK;
+    if (h->nw_alloc >= nw && h->d_visited) return MSBFS_OK;
     msbfs_release_traversal(h);
     cudaStream_t s = h->stream;
     const size_t word_bytes = (size_t)std::max(h->n_pad, 32) * nw * sizeof(ull);
@@ -1321,6 +1323,23 @@ void msbfs_release_traversal(msbfs_handle* h) {
 }
 
 int msbfs_traverse(msbfs_handle* h) { return traverse_impl(h, false, nullptr); }
+
+/* Called at the end of a graph build: size the traversal state for the widest lane word
+ * while the clock is still in the preprocessing window (the reference allocates its
+ * distance array there too, main.cu:295).  Best effort — when memory is short the state
+ * is sized on the first run instead, for the width that run needs. */
+void msbfs_prealloc_traversal(msbfs_handle* h) {
+    if (!h->has_graph || h->n_active == 0) return;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return; }
+    const size_t need = (size_t)h->n_pad * MSBFS_MAX_NW * sizeof(ull) * 4 + (size_t)h->blk_multi * 32 * MSBFS_MAX_NW * sizeof(ull);
+    if (need + (need >> 1) > free_b) return;
+    if (ensure_traversal_buffers(h, MSBFS_MAX_NW) != MSBFS_OK) {
+        cudaGetLastError();
+        msbfs_release_traversal(h);
+        msbfs_clear_error();
+    }
+}
 
 int msbfs_reached_entries_impl(msbfs_handle* h, int64_t* out_entries, int32_t count) {
     std::vector<ull> reached;
