@@ -56,6 +56,8 @@ int msbfs_destroy(msbfs_t* h);
  *                level runs top-down while alpha * (frontier_entries + 0.8 frontier_vertices)
  *                < unexplored_entries + alpha * unexplored_vertices
  *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off
+ *   "reorder"    1 = run the groups heaviest-first (sum of their sources' degrees) so that groups
+ *                with hubs among their sources share batches (default), 0 = caller's order
  *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile) */
 int msbfs_set_option(msbfs_t* h, const char* key, int64_t value);
 
@@ -95,6 +97,13 @@ int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_t* group_of
                          const int32_t* sources);
 int msbfs_run_resident(msbfs_t* h);
 int msbfs_download_sums(msbfs_t* h, int64_t* out_sums, int32_t count);
+
+/* Degrees (CSR row lengths, both directions counted, main.cu:114-115) of `count` vertices
+ * given by their file ids; ids outside [0, n) give 0.  Host arrays.  Lets a scheduler
+ * estimate how heavy a group is (a source with a million neighbours floods the frontier
+ * of its whole batch) before it deals groups out to ranks; the reference's round-robin,
+ * main.cu:303-307, has no such notion. */
+int msbfs_vertex_degrees(msbfs_t* h, int64_t count, const int32_t* vertex_ids, int64_t* out_degrees);
 
 /* Measurement metadata, not part of the reference's output: for the groups of the
  * last run, the number of CSR entries of reached vertices (Graph500 traversed
@@ -137,6 +146,9 @@ int msbfs_argmin(int32_t num_groups, const int64_t* sums, int32_t* min_k_out, in
  * MSBFS_ERR_RANGE when an id needs more than 24 bits or a sum more than 39. */
 int msbfs_argmin_packed(const int64_t* sums, int32_t first_qid, int32_t count, uint64_t* packed_out);
 int msbfs_unpack_argmin(uint64_t packed, int32_t* min_k_out, int64_t* min_f_out);
+/* Same packing for a share whose groups are not contiguous: group i of the share has the
+ * global query id query_ids[i]. */
+int msbfs_argmin_packed_ids(const int64_t* sums, const int32_t* query_ids, int32_t count, uint64_t* packed_out);
 
 /* One 8-byte min all-reduce over NCCL (replaces MPI_Gather + MPI_Gatherv,
  * main.cu:340-365) when every rank owns its own GPU.  `nccl_comm` is an

@@ -93,9 +93,11 @@ SIGNATURES = {
     "msbfs_run_resident": (C.c_int, [C.c_void_p]),
     "msbfs_download_sums": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "msbfs_reached_entries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "msbfs_vertex_degrees": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "msbfs_small_run_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "msbfs_argmin": (C.c_int, [C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_argmin_packed": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_uint64)]),
+    "msbfs_argmin_packed_ids": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint64)]),
     "msbfs_unpack_argmin": (C.c_int, [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_allreduce_min_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
     "msbfs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
@@ -217,6 +219,14 @@ def argmin_packed(sums: np.ndarray, first_qid: int) -> int:
     return out.value
 
 
+def argmin_packed_ids(sums: np.ndarray, query_ids: np.ndarray) -> int:
+    sums = np.ascontiguousarray(sums, dtype=np.int64)
+    ids = np.ascontiguousarray(query_ids, dtype=np.int32)
+    out = C.c_uint64()
+    _check(lib().msbfs_argmin_packed_ids(_ptr(sums) if sums.size else None, _ptr(ids) if ids.size else None, sums.size, C.byref(out)))
+    return out.value
+
+
 def unpack_argmin(packed: int):
     k, f = C.c_int32(), C.c_int64()
     _check(lib().msbfs_unpack_argmin(C.c_uint64(packed), C.byref(k), C.byref(f)))
@@ -237,6 +247,50 @@ def shard_range(num_groups: int, rank: int, world: int, lanes: int = 512):
     per = ((num_groups + world - 1) // world + 63) // 64 * 64
     lo = min(rank * per, num_groups)
     return lo, min(lo + per, num_groups)
+
+
+def deal_groups(costs: np.ndarray, rank: int, world: int) -> np.ndarray:
+    """Group indices sorted heaviest first (ties by index), every world-th starting at `rank`;
+    ``deal_groups(costs, 0, 1)`` is the whole order.  With costs = sum of a group's sources'
+    degrees the order ranks groups by how fast their BFS reaches the hubs; batches cut from
+    consecutive runs of it hold lanes that advance together, which is what lets the bottom-up
+    kernels stop early for the whole batch.  Any assignment gives the same sums and argmin."""
+    order = np.lexsort((np.arange(costs.size), -np.asarray(costs, dtype=np.int64)))
+    return order[rank::world]
+
+
+def plan_shares(costs: np.ndarray, world: int):
+    """(share, lanes): share[r] = group indices rank r runs, `lanes` = batch width to ask the
+    engine for (0 = its own choice).  The heaviest-first order is cut into batches of 512
+    groups — or 256 when that leaves a rank fewer than two batches — and the batches are
+    handed out in snake order (0..W-1, W-1..0, ...), so every rank gets fast batches (hub
+    sources) and slow ones (sources far from the hubs) and finishes with the others."""
+    order = deal_groups(costs, 0, 1)
+    k = int(order.size)
+    lanes = 512
+    if world > 1 and (k + lanes - 1) // lanes < 2 * world:
+        lanes = 256
+    while lanes > 64 and world > 1 and (k + lanes - 1) // lanes < world:
+        lanes //= 2
+    if world == 1:
+        return [order], 0
+    nb = (k + lanes - 1) // lanes
+    owner = []
+    for b in range(nb):
+        lap, pos = divmod(b, world)
+        owner.append(pos if lap % 2 == 0 else world - 1 - pos)
+    share = [np.concatenate([order[b * lanes:(b + 1) * lanes] for b in range(nb) if owner[b] == r] or [np.zeros(0, np.int64)])
+             for r in range(world)]
+    return share, lanes
+
+
+def gather_groups(offsets: np.ndarray, sources: np.ndarray, index: np.ndarray):
+    """(offsets, sources) of the groups `index`, in that order."""
+    sizes = (offsets[1:] - offsets[:-1])[index]
+    new_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    parts = [sources[offsets[i]:offsets[i + 1]] for i in index]
+    new_src = np.concatenate(parts).astype(np.int32) if len(parts) and new_off[-1] else np.zeros(0, np.int32)
+    return new_off, new_src
 
 
 # --------------------------------------------------------------------------- engine
@@ -324,6 +378,13 @@ class Engine:
         out = np.empty(max(k, 1), dtype=np.int64)
         _check(lib().msbfs_reached_entries(self._h, _ptr(out), k))
         return out[:k]
+
+    def vertex_degrees(self, vertex_ids: np.ndarray) -> np.ndarray:
+        ids = np.ascontiguousarray(vertex_ids, dtype=np.int32)
+        out = np.zeros(max(ids.size, 1), dtype=np.int64)
+        if ids.size:
+            _check(lib().msbfs_vertex_degrees(self._h, ids.size, _ptr(ids), _ptr(out)))
+        return out[: ids.size]
 
     def stats(self) -> dict:
         st = Stats()

@@ -160,6 +160,11 @@ struct msbfs_handle {
     int64_t q_cap_groups = 0, q_cap_sources = 0;
     long long* h_pinned_io = nullptr; /* pinned staging for queries in / sums out */
     size_t h_pinned_io_bytes = 0;
+    /* groups run in the order q_order (run position -> caller's index), heaviest first, so that
+     * groups whose sources include hubs share batches; empty = caller's order */
+    std::vector<int32_t> q_order;
+    long long* d_deg = nullptr;
+    int64_t deg_cap = 0;
     unsigned long long* d_scalar = nullptr; /* 8-byte scratch for the packed min all-reduce */
 
     /* pinned staging buffers of the loader (api.cu), allocated on first use */
@@ -171,6 +176,7 @@ struct msbfs_handle {
     int opt_deg_thread = MSBFS_DEG_G8, opt_deg_warp = MSBFS_DEG_WARP, opt_deg_heavy = MSBFS_DEG_HEAVY; /* bin limits (next graph load) */
     int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
     int opt_streak_max_deg = 256;              /* longest row for which the persistent kernel is used */
+    int opt_reorder = 1;                       /* run groups heaviest-first (by their sources' degrees) */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     long long opt_alpha = 40;

@@ -168,6 +168,23 @@ extern "C" int msbfs_argmin_packed(const int64_t* sums, int32_t first_qid, int32
     return MSBFS_OK;
 }
 
+extern "C" int msbfs_argmin_packed_ids(const int64_t* sums, const int32_t* query_ids, int32_t count, uint64_t* packed_out) {
+    if (count < 0 || (count > 0 && (!sums || !query_ids)) || !packed_out)
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_argmin_packed_ids: bad argument");
+    uint64_t best = UINT64_MAX;
+    for (int32_t i = 0; i < count; ++i) {
+        if (sums[i] < 0) continue;
+        if (query_ids[i] < 0 || query_ids[i] >= ((int32_t)1 << kIdBits))
+            return msbfs_fail(MSBFS_ERR_RANGE, "query id %d does not fit %d bits", query_ids[i], kIdBits);
+        if (sums[i] >= ((int64_t)1 << (63 - kIdBits)))
+            return msbfs_fail(MSBFS_ERR_RANGE, "distance sum %lld does not fit the packed word", (long long)sums[i]);
+        const uint64_t w = ((uint64_t)sums[i] << kIdBits) | (uint64_t)query_ids[i];
+        if (w < best) best = w;
+    }
+    *packed_out = best;
+    return MSBFS_OK;
+}
+
 extern "C" int msbfs_unpack_argmin(uint64_t packed, int32_t* min_k_out, int64_t* min_f_out) {
     if (!min_k_out || !min_f_out) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_unpack_argmin: null argument");
     if (packed == UINT64_MAX) { *min_k_out = -1; *min_f_out = -1; return MSBFS_OK; } /* K = 0, main.cu:379-380 */

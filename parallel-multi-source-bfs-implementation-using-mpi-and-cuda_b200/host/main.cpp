@@ -10,8 +10,8 @@
  *   - every rank loads the graph itself through the pinned/async loader and builds
  *     the CSR on its GPU (no host CSR, no MPI_Bcast of up to 8 GiB, main.cu:237-255);
  *   - queries are read by every rank (a few KB; replaces 2K broadcasts, main.cu:264-280);
- *   - ranks take contiguous blocks of whole lane batches (512 groups) instead of round-robin
- *     single queries (main.cu:303-307);
+ *   - groups are ordered by their sources' degrees and handed to the ranks in contiguous runs of
+ *     512-lane batches instead of round-robin single queries (main.cu:303-307);
  *   - the (q, F) Pair gather + scatter + two-pass argmin (main.cu:324-397) becomes one
  *     8-byte unsigned-min all-reduce of (F << 24 | q).
  * Opt-in extras that leave the default output untouched:
@@ -22,6 +22,7 @@
 
 #include "msbfs.h"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -103,24 +104,56 @@ int main(int argc, char* argv[]) {
     /* ---- computation window (main.cu:301 -> 399) ---------------------------- */
     auto start_computation = chrono::high_resolution_clock::now();
 
-    /* contiguous shares: whole 512-lane batches per rank, or — with fewer batches than ranks —
-     * an even split in multiples of 64 lanes so that no GPU idles */
-    const int lanes = 512;
-    const int64_t batches = ((int64_t)K + lanes - 1) / lanes;
-    int32_t first, last;
-    if (batches >= world_size) {
-        const int64_t b0 = batches * world_rank / world_size, b1 = batches * (world_rank + 1) / world_size;
-        first = (int32_t)min<int64_t>(b0 * lanes, K);
-        last = (int32_t)min<int64_t>(b1 * lanes, K);
-    } else {
-        const int64_t per = (((int64_t)K + world_size - 1) / world_size + 63) / 64 * 64;
-        first = (int32_t)min<int64_t>(per * world_rank, K);
-        last = (int32_t)min<int64_t>((int64_t)first + per, K);
+    /* Scheduler (replaces the round-robin of main.cu:303-307).  Groups are ordered by the sum of
+     * their sources' degrees, heaviest first — a proxy for how fast a group's BFS reaches the
+     * hubs — and the order is cut into batches that are handed to the ranks.  Lanes that advance together finish
+     * their levels together, so the bottom-up kernels can stop early for the whole batch.  Every
+     * rank computes the same order from the same inputs; no communication is needed. */
+    vector<int32_t> my_ids;
+    int batch_lanes = 0; /* 0 = the engine's own choice */
+    {
+        const int64_t total = K > 0 ? q_offsets[K] : 0;
+        vector<int64_t> deg((size_t)max<int64_t>(total, 1), 0);
+        if (total > 0 && msbfs_vertex_degrees(eng, total, q_sources, deg.data()) != MSBFS_OK)
+            die(world_rank, "msbfs_vertex_degrees");
+        vector<int64_t> cost((size_t)max(K, 1), 0);
+        for (int32_t g = 0; g < K; ++g)
+            for (int64_t i = q_offsets[g]; i < q_offsets[g + 1]; ++i) cost[(size_t)g] += deg[(size_t)i];
+        vector<int32_t> order((size_t)K);
+        for (int32_t g = 0; g < K; ++g) order[(size_t)g] = g;
+        stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) { return cost[(size_t)x] > cost[(size_t)y]; });
+        /* batches of 512 groups of that order (256 when a rank would get fewer than two, less when
+         * there are fewer batches than ranks), handed out in snake order 0..R-1, R-1..0, ... so that
+         * every rank gets fast and slow batches */
+        if (world_size > 1) {
+            batch_lanes = 512;
+            if (((int64_t)K + batch_lanes - 1) / batch_lanes < 2 * (int64_t)world_size) batch_lanes = 256;
+            while (batch_lanes > 64 && ((int64_t)K + batch_lanes - 1) / batch_lanes < world_size) batch_lanes /= 2;
+            const int64_t nb = ((int64_t)K + batch_lanes - 1) / batch_lanes;
+            for (int64_t b = 0; b < nb; ++b) {
+                const int64_t lap = b / world_size, pos = b % world_size;
+                const int64_t owner = (lap % 2 == 0) ? pos : world_size - 1 - pos;
+                if (owner != world_rank) continue;
+                const int64_t lo = b * batch_lanes, hi = min<int64_t>(lo + batch_lanes, K);
+                my_ids.insert(my_ids.end(), order.begin() + lo, order.begin() + hi);
+            }
+        } else {
+            my_ids = order;
+        }
     }
-    const int32_t mine = last - first;
+    if (batch_lanes && msbfs_set_option(eng, "lanes", batch_lanes) != MSBFS_OK) die(world_rank, "lanes");
+    const int32_t mine = (int32_t)my_ids.size();
+    vector<int64_t> my_offsets((size_t)mine + 1, 0);
+    vector<int32_t> my_sources;
+    for (int32_t p = 0; p < mine; ++p) {
+        const int32_t g = my_ids[(size_t)p];
+        my_sources.insert(my_sources.end(), q_sources + q_offsets[g], q_sources + q_offsets[g + 1]);
+        my_offsets[(size_t)p + 1] = (int64_t)my_sources.size();
+    }
+    if (my_sources.empty()) my_sources.push_back(0);
 
     vector<int64_t> local_F((size_t)max(mine, 1), 0);
-    if (mine > 0 && msbfs_run(eng, mine, q_offsets + first, q_sources, local_F.data()) != MSBFS_OK)
+    if (mine > 0 && msbfs_run(eng, mine, my_offsets.data(), my_sources.data(), local_F.data()) != MSBFS_OK)
         die(world_rank, "msbfs_run");
 
     /* one 8-byte min all-reduce of (F << 24 | id); when a sum or an id does not fit the packed
@@ -128,19 +161,19 @@ int main(int argc, char* argv[]) {
     int32_t minK = -1;
     int64_t minF = -1; /* K = 0 keeps (-1, -1), main.cu:379-380 */
     uint64_t packed = UINT64_MAX;
-    int packable = msbfs_argmin_packed(local_F.data(), first, mine, &packed) == MSBFS_OK ? 1 : 0;
+    int packable = msbfs_argmin_packed_ids(local_F.data(), my_ids.data(), mine, &packed) == MSBFS_OK ? 1 : 0;
     MPI_Allreduce(MPI_IN_PLACE, &packable, 1, MPI_INT, MPI_MIN, MPI_COMM_WORLD);
     if (packable) {
         unsigned long long best = packed;
         MPI_Allreduce(MPI_IN_PLACE, &best, 1, MPI_UNSIGNED_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
         msbfs_unpack_argmin((uint64_t)best, &minK, &minF);
     } else {
-        int32_t lk = -1;
-        int64_t lf = -1;
-        msbfs_argmin(mine, local_F.data(), &lk, &lf);
-        long long gf = lk >= 0 ? lf : INT64_MAX;
+        long long gf = INT64_MAX;
+        for (int32_t p = 0; p < mine; ++p) gf = min<long long>(gf, local_F[(size_t)p]);
         MPI_Allreduce(MPI_IN_PLACE, &gf, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
-        long long gk = (lk >= 0 && lf == gf) ? (long long)first + lk : INT64_MAX;
+        long long gk = INT64_MAX;
+        for (int32_t p = 0; p < mine; ++p)
+            if (local_F[(size_t)p] == gf) gk = min<long long>(gk, my_ids[(size_t)p]);
         MPI_Allreduce(MPI_IN_PLACE, &gk, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
         if (gk != INT64_MAX) { minK = (int32_t)gk; minF = gf; }
     }
@@ -165,13 +198,18 @@ int main(int argc, char* argv[]) {
         int c = mine;
         MPI_Gather(&c, 1, MPI_INT, counts.data(), 1, MPI_INT, 0, MPI_COMM_WORLD);
         for (int i = 1; i < world_size; ++i) displs[(size_t)i] = displs[(size_t)i - 1] + counts[(size_t)i - 1];
-        vector<long long> all((size_t)max(K, 1));
-        MPI_Gatherv(local_F.data(), mine, MPI_LONG_LONG, all.data(), counts.data(), displs.data(), MPI_LONG_LONG, 0,
+        vector<long long> all_f((size_t)max(K, 1));
+        vector<int> all_id((size_t)max(K, 1)), ids_int(my_ids.begin(), my_ids.end());
+        if (ids_int.empty()) ids_int.push_back(0);
+        MPI_Gatherv(local_F.data(), mine, MPI_LONG_LONG, all_f.data(), counts.data(), displs.data(), MPI_LONG_LONG, 0,
                     MPI_COMM_WORLD);
+        MPI_Gatherv(ids_int.data(), mine, MPI_INT, all_id.data(), counts.data(), displs.data(), MPI_INT, 0, MPI_COMM_WORLD);
         if (world_rank == 0) {
+            vector<long long> by_group((size_t)max(K, 1), -1);
+            for (int32_t i = 0; i < K; ++i) by_group[(size_t)all_id[(size_t)i]] = all_f[(size_t)i];
             FILE* f = fopen(dumpFile.c_str(), "w");
             if (f) {
-                for (int32_t k = 0; k < K; ++k) fprintf(f, "%d %lld\n", k, all[(size_t)k]);
+                for (int32_t k = 0; k < K; ++k) fprintf(f, "%d %lld\n", k, by_group[(size_t)k]);
                 fclose(f);
             }
         }

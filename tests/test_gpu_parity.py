@@ -20,6 +20,7 @@ def engine(pkg):
 
 
 def _reset(eng):
+    eng.set_option("reorder", 1)
     eng.set_option("lanes", 0)
     eng.set_option("direction", 0)
     eng.set_option("alpha", 8)
@@ -36,9 +37,11 @@ def test_golden_all_modes(pkg, ob, expected, engine, name):
             for direction in (0, 1, 2):
                 engine.set_option("lanes", lanes)
                 engine.set_option("direction", direction)
-                rep = engine.solve(offs, src)
-                assert rep.sums.tolist() == case["sums"], (lanes, direction)
-                assert rep.min_k + 1 == case["k_printed"] and rep.min_f == case["min_f"]
+                for reorder in ((1, 0) if lanes == 0 else (1,)):  # heaviest-first run order / caller's order
+                    engine.set_option("reorder", reorder)
+                    rep = engine.solve(offs, src)
+                    assert rep.sums.tolist() == case["sums"], (lanes, direction, reorder)
+                    assert rep.min_k + 1 == case["k_printed"] and rep.min_f == case["min_f"]
     finally:
         _reset(engine)
 

@@ -26,8 +26,14 @@ def _worker(rank, world, port, sums, lanes, out_path):
     pkg = graft.load_package()
     sharding = importlib.import_module(pkg.__name__ + ".sharding")
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
-    a, b = pkg.shard_range(len(sums), rank, world, lanes)
-    k, f = sharding.distributed_argmin(np.asarray(sums[a:b], dtype=np.int64), a)
+    if lanes > 0:   # contiguous shares
+        a, b = pkg.shard_range(len(sums), rank, world, lanes)
+        k, f = sharding.distributed_argmin(np.asarray(sums[a:b], dtype=np.int64), a)
+    else:           # groups dealt by cost: non-contiguous ids travel in the packed word
+        costs = np.asarray([(7 * i) % 5 for i in range(len(sums))], dtype=np.int64)
+        mine = pkg.deal_groups(costs, rank, world)
+        packed = pkg.argmin_packed_ids(np.asarray(sums, dtype=np.int64)[mine], mine)
+        k, f = pkg.unpack_argmin(sharding.allreduce_packed_min(packed))
     if rank == 0:
         with open(out_path, "w") as fh:
             fh.write(f"{k} {f}")
@@ -35,11 +41,15 @@ def _worker(rank, world, port, sums, lanes, out_path):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,case", [(2, "ties"), (2, "empty"), (3, "random"), (2, "single_batch"), (3, "too_big_to_pack")])
+@pytest.mark.parametrize("world,case", [(2, "ties"), (2, "empty"), (3, "random"), (2, "single_batch"), (3, "too_big_to_pack"),
+                                        (3, "dealt_ties")])
 def test_distributed_argmin(pkg, ob, tmp_path, world, case):
     rng = np.random.default_rng(5)
     lanes = 4  # small batches so that several ranks own groups
-    if case == "ties":
+    if case == "dealt_ties":
+        lanes = 0
+        sums = [9, 7, 8, 7, 7, 30, 7, 12, 7, 7, 11]
+    elif case == "ties":
         sums = [9, 7, 8, 7, 7, 30, 7, 12, 7]
     elif case == "empty":
         sums = []
