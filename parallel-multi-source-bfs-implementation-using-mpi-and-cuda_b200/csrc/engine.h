@@ -12,9 +12,9 @@
  *                                  ascending = highest-degree neighbour first
  *   visited / cur / nxt / acc      lane words, n_pad x NW x uint64.  Bit j of a
  *                                  vertex's word belongs to query group (lane) j of
- *                                  the running batch.  NW = 1, 2 or 4 (64/128/256
+ *                                  the running batch.  NW = 1, 2, 4 or 8 (64 ... 512
  *                                  lanes); at NW = 4 a word is one 32-byte sector
- *                                  and moves as a single LDG/STG.256.
+ *                                  and moves as a single LDG/STG.256, at NW = 8 two.
  *   cur_nz / nxt_nz / vis_full     bitmaps, one bit per vertex: frontier word is
  *                                  non-zero / all batch lanes have visited it.  A
  *                                  cur/nxt word is only meaningful when its bit is
@@ -34,7 +34,7 @@
 #include <cstdint>
 #include <vector>
 
-constexpr int MSBFS_MAX_NW      = 8;     /* 512 lanes (experimental; 256 is the default ceiling) */
+constexpr int MSBFS_MAX_NW      = 8;     /* 512 lanes: the automatic choice above 256 groups */
 constexpr int MSBFS_MAX_LANES   = 64 * MSBFS_MAX_NW;
 constexpr int MSBFS_CHUNK       = 1024;  /* CSR entries per heavy-row chunk (one warp) */
 constexpr int MSBFS_DEG_HEAVY   = 1024;  /* deg >= this: row is split into chunks      */

@@ -7,7 +7,7 @@
  * BFSKernal main.cu:16-38 and three blocking runtime calls per BFS level) and
  * ComputeFofU (main.cu:75-89, a D2H copy of all distances and a serial host sum).
  *
- * Up to 256 query groups ("lanes") advance together.  Per vertex, bit j of a lane
+ * Up to 512 query groups ("lanes") advance together.  Per vertex, bit j of a lane
  * word says something about group j: visited, in the current frontier, in the next
  * frontier.  A BFS level is then, for every vertex, an OR over neighbours' frontier
  * words; one pass over the CSR serves all lanes.  Distances are never stored: a
