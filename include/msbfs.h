@@ -50,7 +50,7 @@ int msbfs_create(int device, msbfs_t** out);
 int msbfs_destroy(msbfs_t* h);
 
 /* Tuning / test knobs; unknown keys -> MSBFS_ERR_INVALID.
- *   "lanes"      0 = auto (64/128/256 by group count), or 64 / 128 / 256
+ *   "lanes"      0 = auto (64/128/256/512 by group count), or 64 / 128 / 256 / 512
  *   "direction"  0 = direction-optimizing, 1 = top-down only, 2 = bottom-up only
  *   "alpha"      cost of a top-down CSR entry relative to a bottom-up one (default 40): the next
  *                level runs top-down while alpha * (frontier_entries + 0.8 frontier_vertices)
@@ -58,7 +58,12 @@ int msbfs_destroy(msbfs_t* h);
  *   "l2_persist" 1 = pin frontier bitmaps in L2 with an access-policy window (default), 0 = off
  *   "reorder"    1 = run the groups heaviest-first (sum of their sources' degrees) so that groups
  *                with hubs among their sources share batches (default), 0 = caller's order
- *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile) */
+ *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile)
+ * Layout knobs read at the next graph load (defaults chosen by sweeps):
+ *   "seg"        bottom-up segment length, 0 = by graph size (256 ... 1024)
+ *   "deg_heavy" / "deg_warp" / "deg_thread"   degree limits of the top-down bins
+ * Persistent top-down kernel for short-row (road-like) graphs:
+ *   "streak" 0/1, "streak_max_deg" longest row it accepts (256), "streak_levels" levels per launch */
 int msbfs_set_option(msbfs_t* h, const char* key, int64_t value);
 
 /* ----------------------------------------------------------------- graph -- */

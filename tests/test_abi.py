@@ -148,3 +148,30 @@ def test_shard_ranges_cover_everything(pkg):
                 assert 0 <= a <= b <= k
                 covered += list(range(a, b))
             assert covered == list(range(k))
+
+
+def test_share_planning_and_explicit_id_packing(pkg, ob):
+    """plan_shares: every group lands on exactly one rank, batches keep the heaviest-first
+    order; argmin_packed_ids + a plain min over ranks gives the reference's argmin."""
+    rng = np.random.default_rng(11)
+    for k, world in [(0, 2), (1, 3), (700, 2), (4096, 8), (4096, 4), (1000, 8), (5000, 3)]:
+        costs = rng.integers(0, 50, size=k).astype(np.int64)
+        share, lanes = pkg.plan_shares(costs, world)
+        assert len(share) == world
+        allg = np.concatenate(share) if k else np.zeros(0, np.int64)
+        assert sorted(allg.tolist()) == list(range(k))
+        if world > 1 and k:
+            assert lanes in (64, 128, 256, 512)
+            order = pkg.deal_groups(costs, 0, 1).tolist()
+            pos = {g: i for i, g in enumerate(order)}
+            for sh in share:   # inside a batch the global order is kept
+                for b in range(0, len(sh), lanes):
+                    p = [pos[g] for g in sh[b:b + lanes].tolist()]
+                    assert p == list(range(p[0], p[0] + len(p)))
+        sums = rng.integers(0, 6, size=k).astype(np.int64)
+        packed = [pkg.argmin_packed_ids(sums[sh], sh) for sh in share]
+        assert pkg.unpack_argmin(min(packed)) == ob.argmin(sums)
+    offs = np.array([0, 2, 2, 5, 6], dtype=np.int64)
+    src = np.arange(6, dtype=np.int32)
+    o2, s2 = pkg.gather_groups(offs, src, np.array([2, 0, 1]))
+    assert o2.tolist() == [0, 3, 5, 5] and s2.tolist() == [2, 3, 4, 0, 1]
