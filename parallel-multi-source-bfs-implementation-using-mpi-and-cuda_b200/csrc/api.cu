@@ -303,11 +303,14 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
     if (total > 0)
         MSBFS_CUDA(cudaMemcpyAsync(h->d_q_sources, p_src, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, h->stream));
 
-    /* Run order: heaviest groups first, weight = sum of the degrees of a group's sources.  A
-     * source with a huge neighbourhood floods the shared frontier bitmap of its batch; putting
-     * such groups in the same batch lets their (largely identical) frontiers overlap and keeps
-     * the other batches sparse.  Kronecker-26, 4096 x 16: 198 -> 146 ms per step.  The sums go
-     * back to the caller's order in msbfs_download_sums; no result depends on the order. */
+    /* Run order: heaviest groups first, weight = sum of the degrees of a group's sources — a
+     * cheap proxy for how fast a group's BFS reaches the hubs.  Batches cut from consecutive
+     * runs of that order hold lanes that advance together: they reach the dense levels at the
+     * same depth, so the bottom-up kernels' early exit ("every live lane this vertex misses has
+     * been found") fires for the whole batch instead of waiting for a few slow lanes.
+     * Kronecker-26, 4096 x 16: scanned entries per step 19.5 G -> 14.9 G, lane words fetched
+     * 7.9 G -> 4.3 G, 198 -> 146 ms.  The sums go back to the caller's order in
+     * msbfs_download_sums; no result depends on the order. */
     h->q_order.clear();
     if (h->opt_reorder && num_groups > 1 && total > 0 && h->has_graph && h->n_active > 0) {
         if (total > h->deg_cap) {
