@@ -110,6 +110,14 @@ int msbfs_download_sums(msbfs_t* h, int64_t* out_sums, int32_t count);
  * main.cu:303-307, has no such notion. */
 int msbfs_vertex_degrees(msbfs_t* h, int64_t count, const int32_t* vertex_ids, int64_t* out_degrees);
 
+/* The weight the engine itself orders groups by ("reorder"): per group, the sum over its
+ * sources of (degree + degrees of the source's first 256 neighbours) — how fast the group's
+ * BFS reaches the hubs.  A multi-rank scheduler sorts by it and hands out batches of the
+ * order (host/main.cpp); groups as in msbfs_run, host arrays.  No counterpart in the
+ * reference's round-robin (main.cu:303-307). */
+int msbfs_group_weights(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets, const int32_t* sources,
+                        int64_t* out_weights);
+
 /* Measurement metadata, not part of the reference's output: for the groups of the
  * last run, the number of CSR entries of reached vertices (Graph500 traversed
  * edges = half of it).  Runs an extra device pass when called. */

@@ -94,6 +94,7 @@ SIGNATURES = {
     "msbfs_download_sums": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "msbfs_reached_entries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "msbfs_vertex_degrees": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "msbfs_group_weights": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "msbfs_small_run_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "msbfs_argmin": (C.c_int, [C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_argmin_packed": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_uint64)]),
@@ -385,6 +386,15 @@ class Engine:
         if ids.size:
             _check(lib().msbfs_vertex_degrees(self._h, ids.size, _ptr(ids), _ptr(out)))
         return out[: ids.size]
+
+    def group_weights(self, offsets: np.ndarray, sources: np.ndarray) -> np.ndarray:
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        sources = np.ascontiguousarray(sources, dtype=np.int32)
+        k = offsets.size - 1
+        out = np.zeros(max(k, 1), dtype=np.int64)
+        if k:
+            _check(lib().msbfs_group_weights(self._h, k, _ptr(offsets), _ptr(sources) if sources.size else None, _ptr(out)))
+        return out[:k]
 
     def stats(self) -> dict:
         st = Stats()

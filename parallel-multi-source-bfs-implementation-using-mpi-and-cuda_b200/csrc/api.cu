@@ -87,6 +87,28 @@ __global__ void degree_lookup_kernel(const int* __restrict__ ids, long long coun
     out[i] = d;
 }
 
+/* Weight of a source for the run order: its degree plus the degrees of its first 256
+ * neighbours (rows are sorted hubs-first, so these are its largest ones) — roughly the size of
+ * the frontier two levels after the source, i.e. how fast its BFS reaches the hubs. */
+__global__ void degree2_lookup_kernel(const int* __restrict__ ids, long long count, const int* __restrict__ perm, int n,
+                                      int n_active, const long long* __restrict__ row_ptr, const int* __restrict__ col,
+                                      long long* __restrict__ out) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const int s = ids[i];
+    long long d = 0;
+    if ((unsigned)s < (unsigned)n) {
+        const int v = perm[s];
+        if (v < n_active) {
+            const long long b = row_ptr[v], e = row_ptr[v + 1];
+            d = e - b;
+            const long long lim = b + 256 < e ? b + 256 : e;
+            for (long long k = b; k < lim; ++k) { const int u = col[k]; d += row_ptr[u + 1] - row_ptr[u]; }
+        }
+    }
+    out[i] = d;
+}
+
 int set_device(msbfs_handle* h) {
     MSBFS_CUDA(cudaSetDevice(h->device));
     return MSBFS_OK;
@@ -303,8 +325,8 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
     if (total > 0)
         MSBFS_CUDA(cudaMemcpyAsync(h->d_q_sources, p_src, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, h->stream));
 
-    /* Run order: heaviest groups first, weight = sum of the degrees of a group's sources — a
-     * cheap proxy for how fast a group's BFS reaches the hubs.  Batches cut from consecutive
+    /* Run order: heaviest groups first, weight = sum over a group's sources of their two-hop
+     * weight (degree2_lookup_kernel) — a cheap proxy for how fast a group's BFS reaches the hubs.  Batches cut from consecutive
      * runs of that order hold lanes that advance together: they reach the dense levels at the
      * same depth, so the bottom-up kernels' early exit ("every live lane this vertex misses has
      * been found") fires for the whole batch instead of waiting for a few slow lanes.
@@ -318,8 +340,8 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
             MSBFS_CUDA(cudaMalloc(&h->d_deg, sizeof(long long) * (size_t)total));
             h->deg_cap = total;
         }
-        degree_lookup_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(h->d_q_sources, total, h->d_perm, h->n,
-                                                                                      h->n_active, h->d_row_ptr, h->d_deg);
+        degree2_lookup_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(h->d_q_sources, total, h->d_perm, h->n,
+                                                                                       h->n_active, h->d_row_ptr, h->d_col, h->d_deg);
         long long* p_deg = reinterpret_cast<long long*>(p_src + total + (total & 1));
         MSBFS_CUDA(cudaMemcpyAsync(p_deg, h->d_deg, sizeof(long long) * (size_t)total, cudaMemcpyDeviceToHost, h->stream));
         MSBFS_CUDA(cudaStreamSynchronize(h->stream));
@@ -415,6 +437,39 @@ extern "C" int msbfs_vertex_degrees(msbfs_t* h, int64_t count, const int32_t* ve
     cudaFree(d_ids);
     cudaFree(d_out);
     if (e != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "msbfs_vertex_degrees: %s", cudaGetErrorString(e));
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_group_weights(msbfs_t* h, int32_t num_groups, const int64_t* group_offsets, const int32_t* sources,
+                                   int64_t* out_weights) {
+    if (!h || num_groups < 0 || (num_groups > 0 && (!group_offsets || !out_weights)))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_group_weights: bad argument");
+    if (!h->has_graph) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_group_weights: no graph loaded");
+    if (num_groups == 0) return MSBFS_OK;
+    const int64_t base = group_offsets[0], total = group_offsets[num_groups] - base;
+    if (total < 0 || (total > 0 && !sources)) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_group_weights: bad offsets");
+    for (int32_t g = 0; g < num_groups; ++g) out_weights[g] = 0;
+    if (total == 0 || h->n_active == 0) return MSBFS_OK;
+    int rc = set_device(h);
+    if (rc) return rc;
+    int* d_ids = nullptr;
+    long long* d_out = nullptr;
+    MSBFS_CUDA(cudaMalloc(&d_ids, sizeof(int) * (size_t)total));
+    cudaError_t e = cudaMalloc(&d_out, sizeof(long long) * (size_t)total);
+    if (e != cudaSuccess) { cudaFree(d_ids); return msbfs_fail(MSBFS_ERR_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e)); }
+    std::vector<long long> w((size_t)total);
+    e = cudaMemcpyAsync(d_ids, sources + base, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) {
+        degree2_lookup_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(d_ids, total, h->d_perm, h->n, h->n_active,
+                                                                                       h->d_row_ptr, h->d_col, d_out);
+        e = cudaMemcpyAsync(w.data(), d_out, sizeof(long long) * (size_t)total, cudaMemcpyDeviceToHost, h->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_ids);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "msbfs_group_weights: %s", cudaGetErrorString(e));
+    for (int32_t g = 0; g < num_groups; ++g)
+        for (int64_t i = group_offsets[g] - base; i < group_offsets[g + 1] - base; ++i) out_weights[g] += w[(size_t)i];
     return MSBFS_OK;
 }
 

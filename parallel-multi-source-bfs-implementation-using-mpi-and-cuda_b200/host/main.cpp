@@ -104,21 +104,16 @@ int main(int argc, char* argv[]) {
     /* ---- computation window (main.cu:301 -> 399) ---------------------------- */
     auto start_computation = chrono::high_resolution_clock::now();
 
-    /* Scheduler (replaces the round-robin of main.cu:303-307).  Groups are ordered by the sum of
-     * their sources' degrees, heaviest first — a proxy for how fast a group's BFS reaches the
-     * hubs — and the order is cut into batches that are handed to the ranks.  Lanes that advance together finish
+    /* Scheduler (replaces the round-robin of main.cu:303-307).  Groups are ordered by
+     * msbfs_group_weights, heaviest first — a proxy for how fast a group's BFS reaches the hubs — and the order is cut into batches that are handed to the ranks.  Lanes that advance together finish
      * their levels together, so the bottom-up kernels can stop early for the whole batch.  Every
      * rank computes the same order from the same inputs; no communication is needed. */
     vector<int32_t> my_ids;
     int batch_lanes = 0; /* 0 = the engine's own choice */
     {
-        const int64_t total = K > 0 ? q_offsets[K] : 0;
-        vector<int64_t> deg((size_t)max<int64_t>(total, 1), 0);
-        if (total > 0 && msbfs_vertex_degrees(eng, total, q_sources, deg.data()) != MSBFS_OK)
-            die(world_rank, "msbfs_vertex_degrees");
         vector<int64_t> cost((size_t)max(K, 1), 0);
-        for (int32_t g = 0; g < K; ++g)
-            for (int64_t i = q_offsets[g]; i < q_offsets[g + 1]; ++i) cost[(size_t)g] += deg[(size_t)i];
+        if (K > 0 && msbfs_group_weights(eng, K, q_offsets, q_sources, cost.data()) != MSBFS_OK)
+            die(world_rank, "msbfs_group_weights");
         vector<int32_t> order((size_t)K);
         for (int32_t g = 0; g < K; ++g) order[(size_t)g] = g;
         stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) { return cost[(size_t)x] > cost[(size_t)y]; });
