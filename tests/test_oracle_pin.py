@@ -93,3 +93,27 @@ def test_oracle_matches_live_reference(pkg, ob, tmp_path, seed):
         pkg.write_query_file(q1, np.array([0, len(groups[i])], dtype=np.int64), groups[i])
         _, f1, _ = ob.run_reference_host(gpath, q1)
         assert f1 == res.sums[i]
+
+
+def test_oracle_against_an_independent_bfs(ob):
+    """A third opinion: scipy's unweighted shortest paths (multi-source = min over sources)."""
+    import scipy.sparse as sp
+    from scipy.sparse.csgraph import shortest_path
+
+    rng = np.random.default_rng(7)
+    for n, m in [(50, 60), (200, 150), (300, 1200)]:
+        uv = rng.integers(0, n, size=(m, 2)).astype(np.int32)   # duplicates and self-loops included
+        a = sp.coo_matrix((np.ones(m), (uv[:, 0], uv[:, 1])), shape=(n, n))
+        dist = shortest_path(a + a.T, method="D", unweighted=True)
+        csr = ob.Csr(n, uv)
+        for _ in range(10):
+            src = rng.integers(-2, n + 2, size=int(rng.integers(0, 5))).astype(np.int32)
+            valid = src[(src >= 0) & (src < n)]
+            want = np.full(n, -1, dtype=np.int64)
+            if valid.size:
+                d = dist[valid].min(axis=0)
+                want = np.where(np.isfinite(d), d, -1).astype(np.int64)
+            got = ob.distances(csr, src)
+            assert got.tolist() == want.tolist()
+            res = ob.run_csr(csr, np.array([0, src.size], dtype=np.int64), src)
+            assert res.sums[0] == want[want >= 0].sum()
