@@ -175,3 +175,27 @@ def test_share_planning_and_explicit_id_packing(pkg, ob):
     src = np.arange(6, dtype=np.int32)
     o2, s2 = pkg.gather_groups(offs, src, np.array([2, 0, 1]))
     assert o2.tolist() == [0, 3, 5, 5] and s2.tolist() == [2, 3, 4, 0, 1]
+
+
+def test_query_file_round_trip_fuzz(pkg, ob, tmp_path):
+    """Any group structure survives write -> read, in whichever container the writer picks, and
+    the engine's reader and the oracle's reader agree byte for byte."""
+    from hypothesis import given, settings, strategies as st
+
+    groups_st = st.lists(st.lists(st.integers(-(2 ** 31), 2 ** 31 - 1), max_size=300), max_size=300)
+    path = str(tmp_path / "fuzz.bin")
+
+    @settings(max_examples=60, deadline=None)
+    @given(groups_st, st.booleans())
+    def check(groups, force_ext):
+        offs = np.concatenate([[0], np.cumsum([len(g) for g in groups])]).astype(np.int64)
+        src = np.array([x for g in groups for x in g], dtype=np.int64).astype(np.int32)
+        pkg.write_query_file(path, offs, src, force_extended=force_ext)
+        raw = open(path, "rb").read()
+        extended = raw[:8] == b"\x00MSBFSQ2"
+        assert extended == (force_ext or len(groups) > 255 or any(len(g) > 255 for g in groups))
+        for reader in (pkg.load_query_file, ob.load_query_file):
+            o, s = reader(path)
+            assert o.tolist() == offs.tolist() and s.tolist() == src.tolist()
+
+    check()
