@@ -134,11 +134,15 @@ int msbfs_reached_entries(msbfs_t* h, int64_t* out_entries, int32_t count);
  *            (d_row_offsets int64[n + 1], d_col_indices int32), groups as in msbfs_run
  *            (d_group_offsets int64[num_groups + 1] starting at 0, d_sources int32);
  *   output   d_out_sums int64[num_groups];
+ *   none of the pointers may be NULL (pass any valid device pointer for an array that has
+ *   no elements); column entries outside [0, n) are skipped, as out-of-range sources are;
  *   all five are device pointers on the CURRENT device; the work is queued on
  *   `cuda_stream` (a cudaStream_t, NULL = default stream) and the sums are complete when
  *   that stream reaches the end of it — the call itself does not wait.
  * The first call on each device also looks up the array's device address; make that
- * first call before any stream capture.  All calls share the one array (each call
+ * first call before any stream capture.  The address is kept for the life of the process:
+ * a cudaDeviceReset() in between invalidates it, so do not reset a device this entry
+ * point has been used on.  All calls share the one array (each call
  * clears the part it uses before reading it), so calls that overlap on the same GPU —
  * different streams or threads — race with each other: serialise them. */
 int msbfs_small_run_noalloc(int32_t n, const int64_t* d_row_offsets, const int32_t* d_col_indices,
@@ -200,8 +204,10 @@ int msbfs_get_stats(msbfs_t* h, msbfs_stats* out);
  * `ms` is their sum; the counters are always kept.  alg_bytes = 4 B per scanned CSR
  * entry + one lane word per word fetched + (16 B + one word) per vertex examined +
  * two words per word written.  Slots: 0-3 top-down (chunked rows, 32, 8,
- * 2 threads per vertex), 4-7 bottom-up (same bins), 8 top-down finalize, 9 bottom-up
- * chunk finalize, 10 per-lane count, 11 bookkeeping.  Measurement only: nothing in
+ * 2 threads per vertex; 3 is also the persistent short-row kernel), 4 bottom-up long rows
+ * (one thread per segment), 5 bottom-up over hub prefixes (sparse-frontier levels), 6 unused,
+ * 7 bottom-up short rows (one thread per vertex), 8 top-down finalize, 9 bottom-up long-row
+ * finalize, 10 per-lane count, 11 bookkeeping.  Measurement only: nothing in
  * the reference corresponds to it. */
 typedef struct msbfs_kernel_profile {
     char    name[32];

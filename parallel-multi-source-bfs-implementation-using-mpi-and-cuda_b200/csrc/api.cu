@@ -236,6 +236,7 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
 extern "C" int msbfs_set_graph_edges_device(msbfs_t* h, int32_t n, int64_t m, const int32_t* d_uv_pairs) {
     if (!h || n < 0 || m < 0 || (m > 0 && !d_uv_pairs))
         return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_graph_edges_device: bad argument");
+    if (m > MSBFS_MAX_RECORDS) return msbfs_fail(MSBFS_ERR_RANGE, "graph too large (%lld records)", (long long)m);
     int rc = set_device(h);
     if (rc) return rc;
     /* the caller's buffer may have been written on another stream */
@@ -246,6 +247,7 @@ extern "C" int msbfs_set_graph_edges_device(msbfs_t* h, int32_t n, int64_t m, co
 extern "C" int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int32_t* uv_pairs) {
     if (!h || n < 0 || m < 0 || (m > 0 && !uv_pairs))
         return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_set_graph_edges: bad argument");
+    if (m > MSBFS_MAX_RECORDS) return msbfs_fail(MSBFS_ERR_RANGE, "graph too large (%lld records)", (long long)m);
     int rc = set_device(h);
     if (rc) return rc;
     int32_t* d_uv = nullptr;
@@ -272,6 +274,10 @@ extern "C" int msbfs_load_graph_file(msbfs_t* h, const char* path, int32_t* n_ou
     std::memcpy(&n, hdr, 4);       /* main.cu:102 */
     std::memcpy(&m, hdr + 4, 8);   /* main.cu:104 */
     if (n < 0 || m < 0) return msbfs_fail(MSBFS_ERR_FORMAT, "graph file %s has a negative size field", path);
+    /* before m enters any product: 12 + 8 m and 2 m wrap for a crafted header */
+    if (m > MSBFS_MAX_RECORDS)
+        return msbfs_fail(MSBFS_ERR_RANGE, "graph file %s declares %lld records; the limit is %lld", path, (long long)m,
+                          (long long)MSBFS_MAX_RECORDS);
     struct stat stt;
     if (fstat(fd, &stt) == 0 && S_ISREG(stt.st_mode) && (int64_t)stt.st_size < 12 + 8 * m)
         return msbfs_fail(MSBFS_ERR_IO, "graph file %s is truncated: %lld records declared, %lld bytes present", path,
@@ -315,6 +321,11 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
     if (total < 0 || (total > 0 && !sources)) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_upload_queries: bad offsets");
     for (int32_t i = 0; i < num_groups; ++i)
         if (group_offsets[i + 1] < group_offsets[i]) return msbfs_fail(MSBFS_ERR_INVALID, "group offsets must not decrease");
+    /* from here on the previous upload is being overwritten: a failure below must not leave its
+     * group count behind (download_sums / run_resident would hand out stale sums) */
+    h->q_groups = 0;
+    h->q_sources = 0;
+    h->q_order.clear();
     rc = ensure_query_capacity(h, num_groups, total);
     if (rc) return rc;
     /* stage through pinned memory so both copies are truly asynchronous */

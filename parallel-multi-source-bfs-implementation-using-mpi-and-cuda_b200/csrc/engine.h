@@ -34,6 +34,7 @@
 #include <cstdint>
 #include <vector>
 
+constexpr long long MSBFS_MAX_RECORDS = 1ll << 39; /* edge records per graph: 2 m and 8 m stay far from 2^63 */
 constexpr int MSBFS_MAX_NW      = 8;     /* 512 lanes: the automatic choice above 256 groups */
 constexpr int MSBFS_MAX_LANES   = 64 * MSBFS_MAX_NW;
 constexpr int MSBFS_CHUNK       = 1024;  /* CSR entries per heavy-row chunk (one warp) */

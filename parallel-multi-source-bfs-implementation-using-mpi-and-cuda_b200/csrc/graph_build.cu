@@ -137,15 +137,17 @@ void msbfs_release_graph(msbfs_handle* h) {
 
 int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const int32_t* d_uv) {
     if (n < 0 || m < 0) return msbfs_fail(MSBFS_ERR_INVALID, "negative graph size");
-    if (2 * m > ((int64_t)1 << 40)) return msbfs_fail(MSBFS_ERR_INVALID, "graph too large");
-    msbfs_release_graph(h);
-    msbfs_release_traversal(h);
+    if (m > MSBFS_MAX_RECORDS) return msbfs_fail(MSBFS_ERR_RANGE, "graph too large (%lld records)", (long long)m);
     cudaStream_t s = h->stream;
     const int T = 256;
 
-    cudaEvent_t ev0, ev1;
-    MSBFS_CUDA(cudaEventCreate(&ev0));
-    MSBFS_CUDA(cudaEventCreate(&ev1));
+    struct EventPair { /* destroyed on every return path */
+        cudaEvent_t a = nullptr, b = nullptr;
+        ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    } evp;
+    MSBFS_CUDA(cudaEventCreate(&evp.a));
+    MSBFS_CUDA(cudaEventCreate(&evp.b));
+    cudaEvent_t ev0 = evp.a, ev1 = evp.b;
     MSBFS_CUDA(cudaEventRecord(ev0, s));
 
     const int64_t nnz = 2 * m;
@@ -172,6 +174,9 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
     MSBFS_CUDA(cudaMemcpyAsync(h_flags, flags.p, 8, cudaMemcpyDeviceToHost, s));
     MSBFS_CUDA(cudaStreamSynchronize(s));
     if (h_flags[0]) return msbfs_fail(MSBFS_ERR_FORMAT, "edge record with a vertex id outside [0, %d)", n);
+    /* the new edge list is valid: only now does the old graph go (a bad file leaves it in place) */
+    msbfs_release_graph(h);
+    msbfs_release_traversal(h);
 
     /* 2. vertices by degree, descending (stable: ties keep ascending file id) */
     if (n > 0) {
@@ -328,8 +333,6 @@ int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const i
     MSBFS_CUDA(cudaEventSynchronize(ev1));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0, ev1);
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
 
     h->n = n; h->m = m; h->nnz = nnz;
     h->n_active = n_active; h->n_pad = n_pad;

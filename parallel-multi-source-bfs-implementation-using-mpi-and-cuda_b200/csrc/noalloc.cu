@@ -71,6 +71,7 @@ __global__ void __launch_bounds__(SMALL_CTA) small_batch_kernel(ull* __restrict_
             if (f == 0ull) continue;
             for (long long e = row[v] + lane; e < row[v + 1]; e += 32) {
                 const int u = col[e];
+                if ((unsigned)u >= (unsigned)n) continue; /* a bad entry must not index past the shared array */
                 const ull d = f & ~visited[u];
                 if (d) atomicOr(&next[u], d);
             }
@@ -120,7 +121,10 @@ extern "C" int msbfs_small_run_noalloc(int32_t n, const int64_t* d_row_offsets, 
                           "msbfs_small_run_noalloc: %d groups exceed the limit of %d per call; use msbfs_run",
                           num_groups, MSBFS_NOALLOC_MAX_GROUPS);
     if (num_groups == 0) return MSBFS_OK;
-    if (!d_row_offsets || !d_group_offsets || !d_out_sums)
+    /* d_col_indices / d_sources may only be NULL when the graph has no entries / the groups have
+     * no sources; their lengths live on the device, so the caller vouches for that — a NULL
+     * here with entries to read would fault inside the kernel, hence the flat refusal */
+    if (!d_row_offsets || !d_group_offsets || !d_out_sums || !d_col_indices || !d_sources)
         return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_small_run_noalloc: null pointer");
 
     int dev = -1;
@@ -139,9 +143,19 @@ extern "C" int msbfs_small_run_noalloc(int32_t n, const int64_t* d_row_offsets, 
         }
         scratch = g_scratch_addr[dev];
     }
+    /* The address is looked up once per device and kept.  cudaDeviceReset() in this process
+     * unloads the module the array belongs to; the kept address is stale after that
+     * (msbfs.h says so) and there is no call that would tell us. */
+    /* An error some earlier call of the caller's left pending is not this call's failure:
+     * report only what the launch itself raises. */
+    const cudaError_t before = cudaPeekAtLastError();
     small_batch_kernel<<<1, SMALL_CTA, 0, static_cast<cudaStream_t>(cuda_stream)>>>(
         scratch, n, reinterpret_cast<const long long*>(d_row_offsets), d_col_indices, num_groups,
         reinterpret_cast<const long long*>(d_group_offsets), d_sources, reinterpret_cast<long long*>(d_out_sums));
-    MSBFS_CUDA(cudaGetLastError());
+    const cudaError_t after = cudaPeekAtLastError();
+    if (after != cudaSuccess && after != before) {
+        cudaGetLastError();
+        return msbfs_fail(MSBFS_ERR_CUDA, "msbfs_small_run_noalloc: launch failed: %s", cudaGetErrorString(after));
+    }
     return MSBFS_OK;
 }

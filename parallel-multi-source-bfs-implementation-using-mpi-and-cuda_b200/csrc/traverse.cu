@@ -771,7 +771,7 @@ __global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelV
  * cooperative kernel keeps one grid resident and runs consecutive top-down levels —
  * expand, finalize + per-lane count, epilogue — separated by grid-wide barriers, until
  * the BFS is done or the direction heuristic asks for a bottom-up level.  Used only when
- * every row is short (max degree <= option "streak_max_deg", default 32), so a frontier vertex is one thread.
+ * every row is short (max degree <= option "streak_max_deg", default 256), so a frontier vertex is one thread.
  * On return the host finds ctrl / verdict exactly as after a normal epilogue, plus the
  * number of levels run (the frontier buffers have swapped that many times). */
 
@@ -1235,7 +1235,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     h->stats.levels_top_down = h->stats.levels_bottom_up = 0;
     h->stats.scanned_top_down = h->stats.scanned_bottom_up = 0;
     h->stats.frontier_vertices = h->stats.candidate_vertices = 0;
-    h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0;
+    h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0; h->stats.bottom_up_ms = 0.0;
     h->level_log.clear();
     static const char* kSlotNames[MSBFS_NUM_SLOTS] = {"td_heavy", "td_expand_g32", "td_expand_g8", "td_expand_g2",
                                                       "bu_segment", "(unused)", "(unused)", "bu_thread",
@@ -1255,21 +1255,22 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     int rc = ensure_traversal_buffers(h, nw);
     if (rc) return rc;
 
-    cudaEvent_t ev0, ev1;
-    MSBFS_CUDA(cudaEventCreate(&ev0));
-    MSBFS_CUDA(cudaEventCreate(&ev1));
-    MSBFS_CUDA(cudaEventRecord(ev0, s));
+    struct EventPair { /* destroyed on every return path */
+        cudaEvent_t a = nullptr, b = nullptr;
+        ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    } evp;
+    MSBFS_CUDA(cudaEventCreate(&evp.a));
+    MSBFS_CUDA(cudaEventCreate(&evp.b));
+    MSBFS_CUDA(cudaEventRecord(evp.a, s));
     if (nw == 1) rc = run_batches<1>(h, want_reached, reached_out);
     else if (nw == 2) rc = run_batches<2>(h, want_reached, reached_out);
     else if (nw == 8) rc = run_batches<8>(h, want_reached, reached_out);
     else rc = run_batches<4>(h, want_reached, reached_out);
-    if (rc) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return rc; }
-    MSBFS_CUDA(cudaEventRecord(ev1, s));
-    MSBFS_CUDA(cudaEventSynchronize(ev1));
+    if (rc) return rc;
+    MSBFS_CUDA(cudaEventRecord(evp.b, s));
+    MSBFS_CUDA(cudaEventSynchronize(evp.b));
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev0, ev1);
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
+    cudaEventElapsedTime(&ms, evp.a, evp.b);
     h->stats.run_ms = ms;
 
     /* per-level log -> totals and algorithmic bytes (DESIGN.md "algorithmic bytes") */
@@ -1289,6 +1290,9 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
             p.vertices_examined = (int64_t)hc.k_examined[i]; p.words_written = (int64_t)hc.k_written[i];
             p.alg_bytes = 4ll * p.scanned + w * p.words_fetched + (16ll + w) * p.vertices_examined + 2ll * w * p.words_written;
         }
+        /* filled only when every launch was timed (option "profile") */
+        h->stats.bottom_up_ms = h->slot_profile[SLOT_BU_HEAVY].ms + h->slot_profile[SLOT_BU_G32].ms +
+                                h->slot_profile[SLOT_BU_G2].ms + h->slot_profile[SLOT_BU_HEAVY_FINALIZE].ms;
     }
     long long bytes = 0;
     for (const LevelLog& l : h->level_log) {
@@ -1310,6 +1314,14 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
 } // namespace
 
 void msbfs_release_traversal(msbfs_handle* h) {
+    if (h->d_bitmaps && h->stream && h->opt_l2_persist) {
+        /* the access-policy window points at memory that is about to be freed */
+        cudaStreamAttrValue attr;
+        std::memset(&attr, 0, sizeof attr);
+        attr.accessPolicyWindow.num_bytes = 0;
+        cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+        cudaGetLastError();
+    }
     cudaFree(h->d_visited); h->d_visited = nullptr;
     cudaFree(h->d_cur); h->d_cur = nullptr;
     cudaFree(h->d_nxt); h->d_nxt = nullptr;

@@ -72,6 +72,20 @@ def test_loader_errors(pkg, engine, tmp_path):
     assert e.value.code == 2
     with pytest.raises(pkg.MsbfsError):
         engine.set_option("lanes", 100)
+    # a crafted 12-byte header whose record count wraps 12 + 8 m and 2 m: refused before any arithmetic
+    import struct
+    for m_bad in (1 << 62, (1 << 61) + 5, (1 << 39) + 1):
+        open(p, "wb").write(struct.pack("<iq", 4, m_bad))
+        with pytest.raises(pkg.MsbfsError) as e:
+            engine.load_graph_file(p)
+        assert e.value.code == 6, e.value.message
+    # a refused file leaves the graph that was loaded before in place
+    uv = np.array([(0, 1), (1, 2)], dtype=np.int32)
+    engine.set_graph_edges(3, uv)
+    pkg.write_graph_file(p, 3, np.array([(0, 9)], dtype=np.int32))
+    with pytest.raises(pkg.MsbfsError):
+        engine.load_graph_file(p)
+    assert engine.run(np.array([0, 1], dtype=np.int64), np.array([0], dtype=np.int32)).tolist() == [3]
 
 
 def test_empty_and_degenerate_graphs(pkg, ob, engine):
