@@ -153,31 +153,54 @@ def oracle_csr(n, uv_host):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
 
+    ob.set_threads(ob.host_threads())  # launchers export OMP_NUM_THREADS=1; state the team size ourselves
     t0 = time.time()
     csr = ob.Csr(n, uv_host, parallel=uv_host.shape[0] > (1 << 24))
-    log(f"[cpu] oracle CSR built in {time.time() - t0:.1f} s")
+    log(f"[cpu] oracle CSR built in {time.time() - t0:.1f} s on {ob.host_threads()} threads")
     return csr
 
 
-def oracle_sample_rate(csr, offs, src, threads, target_seconds):
+def oracle_sample_rate(pkg, csr, offs, src, threads, target_seconds, pick_order=None):
     """Time the oracle port (BFS + sum only, CSR prebuilt) on a bounded sample of groups.
-    Returns (sums, reached_entries, seconds, groups_timed, threads)."""
+    `pick_order`: group ids to draw the sample from, in that order (default: file order).
+    Returns (sums, reached_entries, seconds, group ids timed, threads)."""
     import oracle_binding as ob
 
     k_total = offs.size - 1
-    threads = threads or ob.lib().oracle_num_threads()
+    threads = threads or ob.host_threads()
+    order = np.arange(k_total) if pick_order is None else np.asarray(pick_order)
     # probe with one group per thread, then size the sample for ~target_seconds
     probe = min(k_total, threads)
-    t0 = time.time()
-    res = ob.run_csr(csr, offs[: probe + 1], src, threads)
-    t_probe = max(time.time() - t0, 1e-6)
+
+    def timed(ids):
+        o, s_ = pkg.gather_groups(offs, src, ids)
+        t0 = time.time()
+        r = ob.run_csr(csr, o, s_, threads)
+        return r, max(time.time() - t0, 1e-6)
+
+    res, t_probe = timed(order[:probe])
     rounds = max(1, int(target_seconds / t_probe))
     sample = min(k_total, probe * rounds)
     if sample > probe:
-        t0 = time.time()
-        res = ob.run_csr(csr, offs[: sample + 1], src, threads)
-        t_probe = max(time.time() - t0, 1e-6)
-    return res.sums, res.reached_entries, t_probe, sample, threads
+        res, t_probe = timed(order[:sample])
+    return res.sums, res.reached_entries, t_probe, order[:sample], threads
+
+
+def spread_over_run_order(costs, lanes=512):
+    """Group ids interleaved from the first, a middle and the last batch of the engine's run
+    order (heaviest first): a sample cut from the head of this list checks the hub-source
+    batch, a middle one and the far-from-hub tail, not just the head of the file."""
+    order = np.lexsort((np.arange(costs.size), -np.asarray(costs, dtype=np.int64)))
+    nb = (order.size + lanes - 1) // lanes
+    parts = [order[b * lanes:(b + 1) * lanes] for b in sorted({0, nb // 2, nb - 1})]
+    out = []
+    for i in range(max(len(p_) for p_ in parts)):
+        for p_ in parts:
+            if i < len(p_):
+                out.append(int(p_[i]))
+    seen = set(out)
+    rest = [int(g) for g in order if int(g) not in seen]
+    return np.array(out + rest, dtype=np.int64)
 
 
 def run_reference_arm(args, wl, rank):
@@ -191,7 +214,8 @@ def run_reference_arm(args, wl, rank):
 
     kind = KINDS[wl["kind"]]
     n = pkg.gen_num_vertices(kind, wl["p0"], wl["p1"])
-    cores = os.cpu_count() or 1
+    cores = ob.host_threads()
+    ob.set_threads(cores)
     t0 = time.time()
     uv = make_edges_host(pkg, wl, kind)
     log(f"[ref] edges ready in {time.time() - t0:.1f} s")
@@ -203,7 +227,7 @@ def run_reference_arm(args, wl, rank):
         ranks = max(1, min(cores, 16))
         sample = min(wl["groups"], 255, max(ranks, args.ref_groups))
         csr = ob.Csr(n, uv, parallel=True)
-        reached = ob.run_csr(csr, offs[: sample + 1], src).reached_entries
+        reached = ob.run_csr(csr, offs[: sample + 1], src, cores).reached_entries
         with tempfile.TemporaryDirectory() as tmp:
             g, q = os.path.join(tmp, "g.bin"), os.path.join(tmp, "q.bin")
             pkg.write_graph_file(g, n, uv)
@@ -223,17 +247,39 @@ def run_reference_arm(args, wl, rank):
         sample_desc = (f"first {sample} of {wl['groups']} groups, oracle/_ref/main_host (unmodified main.cu, host build) "
                        f"under mpirun -np {ranks}; its own 'Computation time' line")
     else:
+        # The oracle port with all host threads.  One BFS per thread is the faster layout, but a
+        # round of it must fit the per-step budget (a Kronecker-26 BFS takes a thread ~25 s); when
+        # it does not, groups run one after the other with every thread inside each BFS.
         threads = cores
         csr = oracle_csr(n, uv)
-        for it in range(args.warmup + args.steps):
-            sums, reached, secs, sample, threads = oracle_sample_rate(csr, offs, src, cores, args.cpu_seconds)
+        del uv
+        iters = args.warmup + args.steps
+        budget = max(1.0, args.ref_seconds / iters)
+        o1, s1 = pkg.gather_groups(offs, src, np.arange(1))
+        t0 = time.time()
+        ob.run_csr(csr, o1, s1, threads, wide=True)
+        t_wide = max(time.time() - t0, 1e-6)
+        wide = t_wide * min(threads, 8) > budget   # a round of `threads` single-thread BFS would not fit
+        per_step = max(1, int(budget / t_wide)) if wide else threads * max(1, int(budget / max(t_wide * min(threads, 8), 1e-6)))
+        per_step = min(per_step, wl["groups"])
+        log(f"[ref] one BFS on {threads} threads: {t_wide:.2f} s; {per_step} groups per step, "
+            f"{'all threads inside each BFS' if wide else 'one BFS per thread'}")
+        for it in range(iters):
+            ids = (np.arange(per_step) + it * per_step) % wl["groups"]
+            o_, s_ = pkg.gather_groups(offs, src, ids)
+            t0 = time.time()
+            res = ob.run_csr(csr, o_, s_, threads, wide=wide)
+            secs = max(time.time() - t0, 1e-6)
             if it >= args.warmup:
-                values.append(reached.sum() / 2 / secs / 1e9)
-                qps.append(sample / secs)
+                values.append(res.reached_entries.sum() / 2 / secs / 1e9)
+                qps.append(per_step / secs)
                 step_s.append(secs)
         kind_s, cores_used = "port", threads
-        sample_desc = (f"first {sample} of {wl['groups']} groups, oracle port (oracle/oracle.c, OpenMP over groups); "
-                       "the host build of main.cu cannot load this workload in bounded time")
+        sample = per_step
+        sample_desc = (f"{per_step} of {wl['groups']} groups per step (consecutive groups of the file, a new set each step), "
+                       f"oracle port (oracle/oracle.c), {threads} threads, "
+                       + ("all threads inside each BFS; " if wide else "one BFS per thread; ")
+                       + "the host build of main.cu cannot load this workload in bounded time")
     v = statistics.median(values)
     line = {
         "impl": "reference", "metric": "GTEPS", "value": v, "unit": "GTEPS", "n_gpus": args.gpus, "steps": args.steps,
@@ -466,15 +512,20 @@ def run_ours(args, wl, rank, local_rank, world):
     cpu = None
     parity = None
     if want_cpu:
-        o_sums, o_reached, secs, sample, threads = oracle_sample_rate(oracle_csr(n, uv_host), offs, src,
-                                                                       os.cpu_count() or 1, args.cpu_seconds)
+        import oracle_binding as ob_
+        o_sums, o_reached, secs, ids, threads = oracle_sample_rate(pkg, oracle_csr(n, uv_host), offs, src,
+                                                                    ob_.host_threads(), args.cpu_seconds,
+                                                                    pick_order=spread_over_run_order(costs))
+        sample = int(ids.size)
         cpu = {"value": float(o_reached.sum()) / 2 / secs / 1e9, "unit": "GTEPS", "cores": threads, "kind": "port",
                "queries_per_sec": sample / secs,
-               "sample": f"first {sample} of {K} groups, oracle port (OpenMP over groups), {secs:.1f} s of BFS+sum"}
+               "sample": f"{sample} of {K} groups taken in turn from the first, a middle and the last 512-group batch of the "
+                         f"run order, oracle port (one BFS per thread), {secs:.1f} s of BFS+sum"}
         full_sums = np.zeros(K, np.int64); full_sums[mine] = sums       # back to the file's group order
         full_reached = np.zeros(K, np.int64); full_reached[mine] = reached
-        ok = np.array_equal(o_sums, full_sums[:sample]) and np.array_equal(o_reached, full_reached[:sample])
-        parity = {"groups_checked": int(sample), "bit_exact": bool(ok)}
+        ok = np.array_equal(o_sums, full_sums[ids]) and np.array_equal(o_reached, full_reached[ids])
+        parity = {"groups_checked": sample, "bit_exact": bool(ok),
+                  "groups": "first / middle / last batch of the run order, interleaved"}
         if not ok:
             log("PARITY FAILURE against the oracle on the sampled groups")
 
@@ -507,6 +558,8 @@ def run_ours(args, wl, rank, local_rank, world):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if parity is not None and not parity["bit_exact"]:
+        raise SystemExit(3)  # a fast wrong answer is not a result
 
 
 def main():
@@ -518,6 +571,7 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("MSBFS_BENCH_WORKLOAD", "kron26"), choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work per oracle timing (bounded sample)")
     ap.add_argument("--ref-groups", type=int, default=32, help="groups fed to the reference host build per step")
+    ap.add_argument("--ref-seconds", type=float, default=200.0, help="reference arm: CPU seconds for all its steps together")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--force-port", action="store_true", help="reference arm: always use the oracle port")
     ap.add_argument("--level-log", default="", help="write the per-level counters of the last step (JSON lines)")

@@ -231,6 +231,90 @@ int oracle_run(int32_t n, const int64_t* row, const int32_t* col,
     return err;
 }
 
+/* ------------------------------------------------- one BFS on all threads --- */
+
+/* The same distances as bfs_group, computed the way the reference's kernel does it
+ * (main.cu:16-38, 61-71): level by level, every frontier vertex relaxing its row, a
+ * vertex taken by whichever thread reaches it first (all writers store the same level,
+ * main.cu:30-33).  Host threads take the place of the kernel's threads; a compare-and-swap
+ * claims the vertex so that it enters the next frontier once.  Used where one BFS per
+ * thread (oracle_run) would make a single timing step last half a minute: Kronecker-26
+ * under bench.py --impl reference.  Returns F and the reached CSR entries. */
+static int64_t bfs_group_wide(int32_t n, const int64_t* row, const int32_t* col, const int32_t* sources, int64_t nsrc,
+                              int32_t* dist, int32_t* cur, int32_t* nxt, int nthreads, int64_t* entries_out) {
+    int64_t ncur = 0;
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+    for (int32_t i = 0; i < n; ++i) dist[i] = -1;                /* main.cu:44 */
+    for (int64_t i = 0; i < nsrc; ++i) {
+        int32_t s = sources[i];
+        if (s >= 0 && s < n && dist[s] != 0) { dist[s] = 0; cur[ncur++] = s; } /* main.cu:46-51 */
+    }
+    for (int32_t level = 0; ncur > 0; ++level) {                 /* main.cu:61-71 */
+        int64_t nnext = 0;
+#pragma omp parallel num_threads(nthreads)
+        {
+            enum { LOCAL = 4096 };
+            int32_t buf[LOCAL];
+            int cnt = 0;
+#pragma omp for schedule(dynamic, 64) nowait
+            for (int64_t i = 0; i < ncur; ++i) {
+                const int32_t v = cur[i];
+                for (int64_t e = row[v]; e < row[v + 1]; ++e) {  /* main.cu:26-35 */
+                    const int32_t u = col[e];
+                    if (dist[u] == -1 && __sync_bool_compare_and_swap(&dist[u], -1, level + 1)) {
+                        buf[cnt++] = u;
+                        if (cnt == LOCAL) {
+                            const int64_t at = __sync_fetch_and_add(&nnext, (int64_t)cnt);
+                            memcpy(nxt + at, buf, sizeof(int32_t) * (size_t)cnt);
+                            cnt = 0;
+                        }
+                    }
+                }
+            }
+            if (cnt) {
+                const int64_t at = __sync_fetch_and_add(&nnext, (int64_t)cnt);
+                memcpy(nxt + at, buf, sizeof(int32_t) * (size_t)cnt);
+            }
+        }
+        int32_t* t = cur; cur = nxt; nxt = t;
+        ncur = nnext;
+    }
+    int64_t sum = 0, entries = 0;                                /* main.cu:81-87 */
+#pragma omp parallel for schedule(static) reduction(+:sum, entries) num_threads(nthreads)
+    for (int32_t i = 0; i < n; ++i) {
+        if (dist[i] < 0) continue;
+        sum += dist[i];
+        entries += row[i + 1] - row[i];
+    }
+    if (entries_out) *entries_out = entries;
+    return sum;
+}
+
+/* main.cu:312-322 with the groups walked one after the other (as a rank of the reference
+ * does) and all host threads inside each BFS. */
+int oracle_run_wide(int32_t n, const int64_t* row, const int32_t* col,
+                    int32_t K, const int64_t* offsets, const int32_t* sources,
+                    int64_t* sums_out, int64_t* reached_entries_out, int32_t nthreads) {
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+    nthreads = 1;
+#endif
+    const size_t cap = (size_t)(n > 0 ? n : 1);
+    int32_t* dist = (int32_t*)malloc(sizeof(int32_t) * cap);
+    int32_t* cur = (int32_t*)malloc(sizeof(int32_t) * cap);
+    int32_t* nxt = (int32_t*)malloc(sizeof(int32_t) * cap);
+    if (!dist || !cur || !nxt) { free(dist); free(cur); free(nxt); return -2; }
+    for (int32_t k = 0; k < K; ++k) {
+        int64_t entries = 0;
+        sums_out[k] = bfs_group_wide(n, row, col, sources + offsets[k], offsets[k + 1] - offsets[k], dist, cur, nxt,
+                                     nthreads, &entries);
+        if (reached_entries_out) reached_entries_out[k] = entries;
+    }
+    free(dist); free(cur); free(nxt);
+    return 0;
+}
+
 /* main.cu:379-397 — minF/minK start at -1; first F >= 0 seeds them, then a strict
  * '<' scan keeps the lowest index among equal minima.  K = 0 leaves (-1, -1); the
  * report prints minK + 1 (main.cu:409). */
@@ -243,6 +327,16 @@ void oracle_argmin(int32_t K, const int64_t* sums, int32_t* min_k_out, int64_t* 
         if (sums[i] < minF && sums[i] >= 0) { minF = sums[i]; minK = i; }
     }
     *min_k_out = minK; *min_f_out = minF;
+}
+
+/* Launchers such as torchrun export OMP_NUM_THREADS=1; the timing legs of bench.py state
+ * their own thread count instead of inheriting that. */
+void oracle_set_threads(int nthreads) {
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+#else
+    (void)nthreads;
+#endif
 }
 
 int oracle_num_threads(void) {

@@ -26,8 +26,14 @@ int oracle_group_distances(int32_t n, const int64_t* row, const int32_t* col,
 int oracle_run(int32_t n, const int64_t* row, const int32_t* col,
                int32_t K, const int64_t* offsets, const int32_t* sources,
                int64_t* sums_out, int64_t* reached_entries_out, int32_t nthreads);
+/* same results, groups one after the other, all host threads inside each BFS (level-synchronous,
+ * as the reference's kernel, main.cu:16-38) */
+int oracle_run_wide(int32_t n, const int64_t* row, const int32_t* col,
+                    int32_t K, const int64_t* offsets, const int32_t* sources,
+                    int64_t* sums_out, int64_t* reached_entries_out, int32_t nthreads);
 /* main.cu:379-397 */
 void oracle_argmin(int32_t K, const int64_t* sums, int32_t* min_k_out, int64_t* min_f_out);
+void oracle_set_threads(int nthreads); /* OpenMP team size for the calls that take no count */
 int oracle_num_threads(void);
 void oracle_free(void* p);
 

@@ -37,6 +37,10 @@ def lib() -> C.CDLL:
         h.oracle_group_distances.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         h.oracle_run.restype = C.c_int
         h.oracle_run.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+        h.oracle_run_wide.restype = C.c_int
+        h.oracle_run_wide.argtypes = h.oracle_run.argtypes
+        h.oracle_set_threads.restype = None
+        h.oracle_set_threads.argtypes = [C.c_int]
         h.oracle_argmin.restype = None
         h.oracle_argmin.argtypes = [C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
         h.oracle_num_threads.restype = C.c_int
@@ -88,7 +92,21 @@ def argmin(sums: np.ndarray):
     return k.value, f.value
 
 
-def run_csr(csr: Csr, offsets: np.ndarray, sources: np.ndarray, threads: int = 0) -> Result:
+def host_threads() -> int:
+    """Cores this process may run on (not OMP_NUM_THREADS, which launchers set to 1)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def set_threads(n: int) -> None:
+    lib().oracle_set_threads(int(n))
+
+
+def run_csr(csr: Csr, offsets: np.ndarray, sources: np.ndarray, threads: int = 0, wide: bool = False) -> Result:
+    """F of every group.  wide=False: one BFS per thread; wide=True: groups in turn, all
+    threads inside each BFS (same results)."""
     offsets = np.ascontiguousarray(offsets, dtype=np.int64)
     sources = np.ascontiguousarray(sources, dtype=np.int32)
     if sources.size == 0:
@@ -96,7 +114,8 @@ def run_csr(csr: Csr, offsets: np.ndarray, sources: np.ndarray, threads: int = 0
     k = offsets.size - 1
     sums = np.zeros(max(k, 1), dtype=np.int64)
     reached = np.zeros(max(k, 1), dtype=np.int64)
-    rc = lib().oracle_run(csr.n, C.c_void_p(csr._row.value), C.c_void_p(csr._col.value), k, _p(offsets), _p(sources),
+    fn = lib().oracle_run_wide if wide else lib().oracle_run
+    rc = fn(csr.n, C.c_void_p(csr._row.value), C.c_void_p(csr._col.value), k, _p(offsets), _p(sources),
                           _p(sums), _p(reached), threads)
     if rc != 0:
         raise RuntimeError(f"oracle_run failed with {rc}")

@@ -20,6 +20,13 @@ def test_oracle_matches_reference_golden(pkg, ob, expected, name):
     assert res.sums.tolist() == case["sums"]
     assert res.min_k + 1 == case["k_printed"]  # main.cu:409 prints minK + 1
     assert res.min_f == case["min_f"]
+    # the all-threads-inside-one-BFS mode (bench.py's reference arm at Kronecker-26) and the
+    # parallel CSR build are held to the same vectors
+    csr = ob.Csr(n, uv, parallel=True)
+    for threads in (1, 3):
+        wide = ob.run_csr(csr, offs, src, threads=threads, wide=True)
+        assert wide.sums.tolist() == case["sums"]
+        assert np.array_equal(wide.reached_entries, res.reached_entries)
 
 
 def test_known_answers_by_hand(ob):

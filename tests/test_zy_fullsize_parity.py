@@ -1,0 +1,118 @@
+"""BASELINE.json configs 3, 4 and 5 at FULL size through the C ABI, on the GPU.
+
+For each config the graph is generated on the device (msbfs_gen_edges_device), the whole query
+set is run, and
+  * >= 16 groups are compared bit for bit with the CPU oracle (oracle/oracle.c, pinned to the
+    reference's own code) — picked from the first, a middle and the last batch of the engine's
+    RUN order (heaviest-first), not from the head of the file: the head batch holds the hub
+    sources, the tail batch the groups that reach the hubs last, and they exercise different
+    levels of the direction heuristic;
+  * the argmin of the full run is checked against the oracle's rule (main.cu:379-397) applied
+    to the engine's own sums;
+  * invariances that need no oracle are checked on a slice: F does not depend on the lane
+    width, on the traversal direction or on the run order.
+Semantics matched: /root/reference/main.cu:40-89 (BFS + sum), 379-397 (argmin).
+
+The file name puts these tests after everything except the no-alloc test, so a run that stops at
+the first failure has been through the quick tests first."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GRAPH_SEED, QUERY_SEED = 1, 2  # the seeds bench.py uses: these are the benchmarked inputs
+
+
+def _device_graph(pkg, engine, kind, p0, p1, m):
+    import torch
+
+    n = pkg.gen_num_vertices(kind, p0, p1)
+    buf = torch.empty((m, 2), dtype=torch.int32, device="cuda:0")
+    assert pkg.lib().msbfs_gen_edges_device(0, kind, p0, p1, m, GRAPH_SEED, buf.data_ptr()) == 0
+    engine.set_graph_edges_device(n, m, buf.data_ptr())
+    uv = buf.cpu().numpy()
+    del buf
+    torch.cuda.empty_cache()
+    return n, uv
+
+
+def _run_order(engine, offs, src):
+    w = engine.group_weights(offs, src)
+    return np.lexsort((np.arange(w.size), -w))  # heaviest first, ties by index (stable)
+
+
+def _spread_sample(order, per_part, lanes=512):
+    """Groups from the first, a middle and the last batch of the run order."""
+    k = order.size
+    nb = (k + lanes - 1) // lanes
+    picks = []
+    for b in sorted({0, nb // 2, nb - 1}):
+        part = order[b * lanes:(b + 1) * lanes]
+        idx = np.unique(np.linspace(0, part.size - 1, per_part).astype(int))
+        picks.extend(part[idx].tolist())
+    return np.array(sorted(set(picks)), dtype=np.int64)
+
+
+def _reset(engine):
+    for key, val in (("lanes", 0), ("direction", 0), ("reorder", 1)):
+        engine.set_option(key, val)
+
+
+def _check_config(pkg, ob, engine, kind, p0, p1, m, groups, per_group, per_part, slice_groups, slice_checks):
+    n, uv = _device_graph(pkg, engine, kind, p0, p1, m)
+    offs, src = pkg.gen_queries_host(n, groups, per_group, QUERY_SEED)
+    base = engine.run(offs, src)
+    assert base.size == groups
+
+    # ---- oracle sample spread over the run order
+    order = _run_order(engine, offs, src)
+    pick = _spread_sample(order, per_part)
+    assert pick.size >= 16
+    o_offs, o_src = pkg.gather_groups(offs, src, pick)
+    ob.set_threads(ob.host_threads())
+    csr = ob.Csr(n, uv, parallel=True)
+    del uv
+    want = ob.run_csr(csr, o_offs, o_src, threads=min(ob.host_threads(), int(pick.size)))
+    del csr
+    bad = np.nonzero(base[pick] != want.sums)[0]
+    assert bad.size == 0, f"groups {pick[bad].tolist()}: engine {base[pick][bad].tolist()} oracle {want.sums[bad].tolist()}"
+
+    # ---- argmin rule on the full result
+    assert pkg.argmin(base) == ob.argmin(base)
+
+    # ---- invariances on a slice of the run order's middle (no oracle needed)
+    mid = order[(groups - slice_groups) // 2:(groups - slice_groups) // 2 + slice_groups]
+    s_offs, s_src = pkg.gather_groups(offs, src, mid)
+    try:
+        for key, val in slice_checks:
+            _reset(engine)
+            engine.set_option(key, val)
+            got = engine.run(s_offs, s_src)
+            assert np.array_equal(got, base[mid]), f"F changed with {key}={val}"
+    finally:
+        _reset(engine)
+    return base
+
+
+@pytest.fixture()
+def engine(pkg):
+    with pkg.Engine(0) as eng:
+        yield eng
+
+
+def test_config3_kron26_full_size(pkg, ob, engine):
+    """Graph500 Kronecker scale 26 (2^30 - 1 records), 4096 groups x 16 sources."""
+    _check_config(pkg, ob, engine, pkg.GEN_KRON, 26, 0, (1 << 30) - 1, 4096, 16, per_part=6, slice_groups=512,
+                  slice_checks=[("lanes", 64), ("direction", 2), ("reorder", 0), ("lanes", 256)])
+
+
+def test_config4_lattice4096_full_size(pkg, ob, engine):
+    """4096 x 4096 lattice, 512 groups x 4 sources (thousands of levels, persistent kernel)."""
+    _check_config(pkg, ob, engine, pkg.GEN_LATTICE, 4096, 4096, 2 * 4096 * 4095, 512, 4, per_part=176, slice_groups=128,
+                  slice_checks=[("lanes", 64), ("reorder", 0)])
+
+
+def test_config5_er24_full_size(pkg, ob, engine):
+    """Erdos-Renyi n = 2^24, m = 2^28, 1024 groups x 256 sources (dense early frontiers)."""
+    _check_config(pkg, ob, engine, pkg.GEN_ER, 1 << 24, 0, 1 << 28, 1024, 256, per_part=8, slice_groups=256,
+                  slice_checks=[("lanes", 64), ("direction", 2), ("reorder", 0)])
