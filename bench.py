@@ -512,6 +512,7 @@ def run_ours(args, wl, rank, local_rank, world):
     cpu = None
     parity = None
     if want_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_binding as ob_
         o_sums, o_reached, secs, ids, threads = oracle_sample_rate(pkg, oracle_csr(n, uv_host), offs, src,
                                                                     ob_.host_threads(), args.cpu_seconds,

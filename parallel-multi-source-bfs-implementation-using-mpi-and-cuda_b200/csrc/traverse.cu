@@ -47,6 +47,7 @@ namespace {
 typedef unsigned long long ull;
 
 constexpr int CTA = 256;
+constexpr int HUB_CTA = 512; /* bottom-up kernels with the hub bitmap in shared memory: one block per SM */
 #ifndef MSBFS_NW8_BLOCKS
 #define MSBFS_NW8_BLOCKS 2 /* resident 256-thread blocks per SM asked of the 512-lane bottom-up kernels */
 #endif
@@ -326,53 +327,73 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
  * memory latency (the words) instead of three chained ones (col -> bitmap -> word): these
  * kernels are bound by latency x occupancy, not by bytes (ncu r1f).  Stops as soon as
  * every lane in `need` has been found. */
-template <int NW>
-__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, long long beg, long long end, const LW<NW>& need,
-                                              unsigned& scanned, unsigned& fetched) {
+template <int W> struct alignas(4 * W) ColVec { int v[W]; };
+
+/* W = col entries per load (4: one 128-bit load, 8: one 256-bit load).  HUB: the frontier
+ * bitmap of the first a.hub_words * 32 vertices — the hubs, which is where most col entries
+ * point — has been copied to shared memory by the block; a probe there costs a bank access
+ * instead of one L1 wavefront per distinct 128-byte line (ncu r1/r2e: the four probe
+ * instructions were half of the kernel's L1 wavefronts, 24 tag requests per instruction). */
+template <int NW, int W, bool HUB>
+__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, const unsigned* s_hub, long long beg, long long end,
+                                              const LW<NW>& need, unsigned& scanned, unsigned& fetched) {
+    typedef ColVec<W> CV;
+    auto probe = [&](int v) -> unsigned {
+        const int w = v >> 5;
+        if (HUB && w < a.hub_words) return s_hub[w];
+        return a.cur_nz[w];
+    };
     LW<NW> acc = lw_zero<NW>();
-    long long e4 = beg & ~3ll;
-    int4 c = __ldg(reinterpret_cast<const int4*>(a.col + e4));
-    unsigned m = 0u; /* bit k: entry e4 + k belongs to the segment */
+    long long e = beg & ~(long long)(W - 1);
+    CV c = *reinterpret_cast<const CV*>(a.col + e);
+    unsigned m = 0u; /* bit k: entry e + k belongs to the segment */
 #pragma unroll
-    for (int k = 0; k < 4; ++k) m |= (unsigned)((e4 + k >= beg) && (e4 + k < end)) << k;
-    unsigned bw[4];
-    {
-        const int v[4] = {c.x, c.y, c.z, c.w};
+    for (int k = 0; k < W; ++k) m |= (unsigned)((e + k >= beg) && (e + k < end)) << k;
+    unsigned bw[W];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) bw[k] = ((m >> k) & 1u) ? a.cur_nz[v[k] >> 5] : 0u;
-    }
+    for (int k = 0; k < W; ++k) bw[k] = ((m >> k) & 1u) ? probe(c.v[k]) : 0u;
     for (;;) {
-        const long long e4n = e4 + 4;
-        const bool more = e4n < end;
-        int4 cn = make_int4(0, 0, 0, 0);
-        if (more) cn = __ldg(reinterpret_cast<const int4*>(a.col + e4n));
-        const int v[4] = {c.x, c.y, c.z, c.w};
+        const long long en = e + W;
+        const bool more = en < end;
+        CV cn;
+#pragma unroll
+        for (int k = 0; k < W; ++k) cn.v[k] = 0;
+        if (more) cn = *reinterpret_cast<const CV*>(a.col + en);
         LW<NW> t = lw_zero<NW>();
+        scanned += __popc(m);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const bool in = (m >> k) & 1u;
-            const bool hit = in && ((bw[k] >> (v[k] & 31)) & 1u);
-            scanned += in;
+        for (int k = 0; k < W; ++k) {
+            const bool hit = ((m >> k) & 1u) && ((bw[k] >> (c.v[k] & 31)) & 1u);
             fetched += hit;
-            if (hit) t = lw_or(t, lw_load<NW>(a.cur, v[k]));
+            if (hit) t = lw_or(t, lw_load<NW>(a.cur, c.v[k]));
         }
-        unsigned mn = 0u, bwn[4] = {0u, 0u, 0u, 0u};
-        if (more) {
-            const int vn[4] = {cn.x, cn.y, cn.z, cn.w};
+        unsigned mn = 0u, bwn[W];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const bool in = e4n + k < end;
+        for (int k = 0; k < W; ++k) bwn[k] = 0u;
+        if (more) {
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                const bool in = en + k < end;
                 mn |= (unsigned)in << k;
-                bwn[k] = in ? a.cur_nz[vn[k] >> 5] : 0u;
+                bwn[k] = in ? probe(cn.v[k]) : 0u;
             }
         }
         acc = lw_or(acc, t);
         if (!more || lw_covers(acc, need)) break;
-        c = cn; m = mn; e4 = e4n;
+        c = cn; m = mn; e = en;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) bw[k] = bwn[k];
+        for (int k = 0; k < W; ++k) bw[k] = bwn[k];
     }
     return acc;
+}
+
+/* the block's copy of the hub part of the frontier bitmap (dynamic shared memory) */
+extern __shared__ unsigned s_hub_bits[];
+template <bool HUB> __device__ __forceinline__ void load_hub_bits(const TravArgs& a) {
+    if (HUB) {
+        for (int i = threadIdx.x; i < a.hub_words; i += blockDim.x) s_hub_bits[i] = a.cur_nz[i];
+        __syncthreads();
+    }
 }
 
 /* The block's result bits: nxt_nz is fully rewritten every bottom-up level. */
@@ -387,8 +408,9 @@ __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, in
 /* Rows of at most MSBFS_DEG_G8 entries: one thread per vertex, no cross-thread
  * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
  * each thread leaves its loop as soon as its own need is covered. */
-template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
+template <int NW, int W, bool HUB>
+__global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
+    load_hub_bits<HUB>(a);
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     ull full_acc = 0;
@@ -405,7 +427,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
             const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
             if (lw_any(need)) {
                 ++examined;
-                const LW<NW> acc = bu_scan_row<NW>(a, beg, end, need, scanned, fetched);
+                const LW<NW> acc = bu_scan_row<NW, W, HUB>(a, s_hub_bits, beg, end, need, scanned, fetched);
                 const LW<NW> found = lw_and(acc, need);
                 if (lw_any(found)) {
                     const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
@@ -431,8 +453,9 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
  * and the early segments of a row have usually run before its later ones start.
  * Segments of a row co-operate through hub_acc: a segment first subtracts what earlier
  * segments already found and skips the row when nothing is left to find. */
-template <int NW, int U>
-__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
+template <int NW, int W, bool HUB>
+__global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
+    load_hub_bits<HUB>(a);
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
@@ -457,7 +480,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
         if (!lw_any(need)) continue;
         const long long beg = a.row_ptr[u] + (long long)k * a.seg;
         const long long end = min(beg + (long long)a.seg, a.row_ptr[u + 1]);
-        const LW<NW> acc = bu_scan_row<NW>(a, beg, end, need, scanned, fetched);
+        const LW<NW> acc = bu_scan_row<NW, W, HUB>(a, s_hub_bits, beg, end, need, scanned, fetched);
         const LW<NW> found = lw_and(acc, need);
         if (lw_any(found)) {
 #pragma unroll
