@@ -59,6 +59,8 @@ int msbfs_destroy(msbfs_t* h);
  *   "reorder"    1 = run the groups heaviest-first (sum of their sources' degrees) so that groups
  *                with hubs among their sources share batches (default), 0 = caller's order
  *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile)
+ *   "col_width"  col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the
+ *                long-row kernel of 512-lane batches and 4 elsewhere (default)
  * Layout knobs read at the next graph load (defaults chosen by sweeps):
  *   "seg"        bottom-up segment length, 0 = by graph size (256 ... 1024)
  *   "deg_heavy" / "deg_warp" / "deg_thread"   degree limits of the top-down bins
@@ -167,12 +169,41 @@ int msbfs_unpack_argmin(uint64_t packed, int32_t* min_k_out, int64_t* min_f_out)
  * global query id query_ids[i]. */
 int msbfs_argmin_packed_ids(const int64_t* sums, const int32_t* query_ids, int32_t count, uint64_t* packed_out);
 
-/* One 8-byte min all-reduce over NCCL (replaces MPI_Gather + MPI_Gatherv,
- * main.cu:340-365) when every rank owns its own GPU.  `nccl_comm` is an
- * ncclComm_t; NCCL is resolved at run time (dlopen) so the library itself has no
- * NCCL link dependency.  With several ranks on one device use MPI_Allreduce on
- * the packed word instead. */
+/* One 8-byte min all-reduce over NCCL / NVLink (replaces MPI_Gather + MPI_Gatherv of the
+ * Pair struct and the scan on rank 0, main.cu:166-193, 340-397) when every rank owns its
+ * own GPU.  `nccl_comm` is an ncclComm_t — the caller's own, or one made by
+ * msbfs_nccl_comm_create.  NCCL is resolved at run time (dlopen), so the library has no NCCL
+ * link dependency.  With several ranks on one device (mpirun -np 2 ... -gn 1) NCCL cannot
+ * form a communicator: reduce the packed word with MPI_Allreduce instead. */
 int msbfs_allreduce_min_u64(msbfs_t* h, void* nccl_comm, uint64_t* inout);
+
+/* Communicator bootstrap for a host program that has MPI (or any launcher) but does not
+ * want to link NCCL itself — no counterpart in the reference, which has no NCCL.  Rank 0
+ * calls msbfs_nccl_unique_id and broadcasts the MSBFS_NCCL_ID_BYTES bytes (MPI_Bcast of
+ * MPI_BYTE); every rank then calls msbfs_nccl_comm_create with the same id, the world size
+ * and its rank (collective: all ranks must call it), on the device its handle is bound to. */
+#define MSBFS_NCCL_ID_BYTES 128
+int msbfs_nccl_unique_id(void* id_out);
+int msbfs_nccl_comm_create(msbfs_t* h, const void* id, int32_t world, int32_t rank, void** comm_out);
+int msbfs_nccl_comm_destroy(void* comm);
+
+/* -------------------------------------------------------------- scheduler -- */
+
+/* Replaces the round-robin ownership of main.cu:303-307.  Orders the groups heaviest first by
+ * `weights` (msbfs_group_weights), cuts the order into batches of `lanes` groups and assigns
+ * the batches to `world` ranks: by measured cost (longest first onto the least-loaded rank)
+ * when batch_cost[0 .. num_costs) holds one figure per batch (msbfs_get_batch_ms of an earlier
+ * pass over the same plan, concatenated over ranks in batch order), else in snake order
+ * 0..R-1, R-1..0, ...  Outputs: order_out[i] = group at run position i (all groups);
+ * owner_out[g] = rank that runs group g; *lanes_out = batch width the ranks should set with
+ * msbfs_set_option("lanes") (0 = the engine's own choice, when world == 1).  A rank runs its
+ * groups in the relative order of order_out.  lanes = 0 lets msbfs_plan_lanes choose: 512,
+ * or 256 when that leaves a rank fewer than two batches, halved further while ranks would
+ * stay idle.  Host-only; every rank computes the same plan from the same inputs. */
+int msbfs_plan_lanes(int32_t num_groups, int32_t world);
+int msbfs_plan_shares(int32_t num_groups, const int64_t* weights, int32_t world, int32_t lanes,
+                      const double* batch_cost, int32_t num_costs, int32_t* order_out, int32_t* owner_out,
+                      int32_t* lanes_out);
 
 /* ------------------------------------------------------------ statistics -- */
 
@@ -205,7 +236,7 @@ int msbfs_get_stats(msbfs_t* h, msbfs_stats* out);
  * entry + one lane word per word fetched + (16 B + one word) per vertex examined +
  * two words per word written.  Slots: 0-3 top-down (chunked rows, 32, 8,
  * 2 threads per vertex; 3 is also the persistent short-row kernel), 4 bottom-up long rows
- * (one thread per segment), 5 bottom-up over hub prefixes (sparse-frontier levels), 6 unused,
+ * (one thread per segment), 5-6 unused,
  * 7 bottom-up short rows (one thread per vertex), 8 top-down finalize, 9 bottom-up long-row
  * finalize, 10 per-lane count, 11 bookkeeping.  Measurement only: nothing in
  * the reference corresponds to it. */
@@ -234,6 +265,21 @@ typedef struct msbfs_level_record {
 } msbfs_level_record;
 
 int msbfs_get_level_log(msbfs_t* h, msbfs_level_record* out, int32_t capacity, int32_t* count_out);
+
+/* With option "profile" = 1: every kernel launch of the last run, in launch order, with the
+ * batch and BFS level it belongs to (level -1 = source injection) and its CUDA-event time.
+ * Measurement only (per-level cost of each kernel); nothing in the reference corresponds. */
+typedef struct msbfs_launch_record {
+    int32_t batch;
+    int32_t level;
+    int32_t slot;   /* as in msbfs_get_kernel_profile */
+    float   ms;
+} msbfs_launch_record;
+int msbfs_get_launch_log(msbfs_t* h, msbfs_launch_record* out, int32_t capacity, int32_t* count_out);
+
+/* Device time (CUDA events) of every lane batch of the last run, in run order: what a
+ * multi-rank scheduler needs to plan shares from measured cost (msbfs_plan_shares). */
+int msbfs_get_batch_ms(msbfs_t* h, double* out, int32_t capacity, int32_t* count_out);
 
 int msbfs_num_kernel_slots(void);
 int msbfs_get_kernel_profile(msbfs_t* h, int slot, msbfs_kernel_profile* out);

@@ -65,6 +65,12 @@ class KernelProfile(C.Structure):
         return d
 
 
+class LaunchRecord(C.Structure):
+    """struct msbfs_launch_record (include/msbfs.h)."""
+
+    _fields_ = [("batch", C.c_int32), ("level", C.c_int32), ("slot", C.c_int32), ("ms", C.c_float)]
+
+
 class LevelRecord(C.Structure):
     """struct msbfs_level_record (include/msbfs.h)."""
 
@@ -101,8 +107,16 @@ SIGNATURES = {
     "msbfs_argmin_packed_ids": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint64)]),
     "msbfs_unpack_argmin": (C.c_int, [C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_allreduce_min_u64": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "msbfs_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "msbfs_nccl_comm_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "msbfs_nccl_comm_destroy": (C.c_int, [C.c_void_p]),
+    "msbfs_plan_lanes": (C.c_int, [C.c_int32, C.c_int32]),
+    "msbfs_plan_shares": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                    C.POINTER(C.c_int32)]),
     "msbfs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "msbfs_get_level_log": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
+    "msbfs_get_launch_log": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
+    "msbfs_get_batch_ms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
     "msbfs_num_kernel_slots": (C.c_int, []),
     "msbfs_get_kernel_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(KernelProfile)]),
     "msbfs_load_query_file": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
@@ -260,29 +274,22 @@ def deal_groups(costs: np.ndarray, rank: int, world: int) -> np.ndarray:
     return order[rank::world]
 
 
-def plan_shares(costs: np.ndarray, world: int):
-    """(share, lanes): share[r] = group indices rank r runs, `lanes` = batch width to ask the
-    engine for (0 = its own choice).  The heaviest-first order is cut into batches of 512
-    groups — or 256 when that leaves a rank fewer than two batches — and the batches are
-    handed out in snake order (0..W-1, W-1..0, ...), so every rank gets fast batches (hub
-    sources) and slow ones (sources far from the hubs) and finishes with the others."""
-    order = deal_groups(costs, 0, 1)
-    k = int(order.size)
-    lanes = 512
-    if world > 1 and (k + lanes - 1) // lanes < 2 * world:
-        lanes = 256
-    while lanes > 64 and world > 1 and (k + lanes - 1) // lanes < world:
-        lanes //= 2
-    if world == 1:
-        return [order], 0
-    nb = (k + lanes - 1) // lanes
-    owner = []
-    for b in range(nb):
-        lap, pos = divmod(b, world)
-        owner.append(pos if lap % 2 == 0 else world - 1 - pos)
-    share = [np.concatenate([order[b * lanes:(b + 1) * lanes] for b in range(nb) if owner[b] == r] or [np.zeros(0, np.int64)])
-             for r in range(world)]
-    return share, lanes
+def plan_shares(costs: np.ndarray, world: int, lanes: int = 0, batch_cost=None):
+    """(share, lanes) from msbfs_plan_shares — the one planner, shared with host/main.cpp:
+    share[r] = group indices rank r runs, in run order; `lanes` = batch width to ask the
+    engine for (0 = its own choice).  `batch_cost`: measured cost per batch of the same plan
+    (batch order), if there is one; without it batches go out in snake order."""
+    costs = np.ascontiguousarray(costs, dtype=np.int64)
+    k = int(costs.size)
+    order = np.zeros(max(k, 1), dtype=np.int32)
+    owner = np.zeros(max(k, 1), dtype=np.int32)
+    lanes_out = C.c_int32()
+    bc = None if batch_cost is None else np.ascontiguousarray(batch_cost, dtype=np.float64)
+    _check(lib().msbfs_plan_shares(k, _ptr(costs) if k else None, world, lanes, _ptr(bc) if bc is not None and bc.size else None,
+                                   0 if bc is None else int(bc.size), _ptr(order), _ptr(owner), C.byref(lanes_out)))
+    order, owner = order[:k].astype(np.int64), owner[:k]
+    share = [order[owner[order] == r] for r in range(world)]
+    return share, lanes_out.value
 
 
 def gather_groups(offsets: np.ndarray, sources: np.ndarray, index: np.ndarray):
@@ -406,6 +413,19 @@ class Engine:
         cnt = C.c_int32()
         _check(lib().msbfs_get_level_log(self._h, buf, capacity, C.byref(cnt)))
         return [{name: getattr(buf[i], name) for name, _ in LevelRecord._fields_} for i in range(min(cnt.value, capacity))]
+
+    def launch_log(self, capacity: int = 1 << 16) -> list:
+        buf = (LaunchRecord * capacity)()
+        cnt = C.c_int32()
+        _check(lib().msbfs_get_launch_log(self._h, buf, capacity, C.byref(cnt)))
+        return [{"batch": buf[i].batch, "level": buf[i].level, "slot": buf[i].slot, "ms": buf[i].ms}
+                for i in range(min(cnt.value, capacity))]
+
+    def batch_ms(self, capacity: int = 4096) -> list:
+        buf = (C.c_double * capacity)()
+        cnt = C.c_int32()
+        _check(lib().msbfs_get_batch_ms(self._h, buf, capacity, C.byref(cnt)))
+        return [buf[i] for i in range(min(cnt.value, capacity))]
 
     def kernel_profiles(self) -> list:
         out = []

@@ -1,11 +1,10 @@
 /*
  * api.cu — the extern "C" entry points of include/msbfs.h that touch the GPU:
- * handle life cycle, the streaming loader, query upload / run / download, and the
- * NCCL min-reduction.  Reference lines replaced are cited in include/msbfs.h.
+ * handle life cycle, the streaming loader, query upload / run / download (the NCCL
+ * min-reduction lives in comm.cu).  Reference lines replaced are cited in include/msbfs.h.
  */
 #include "engine.h"
 
-#include <dlfcn.h>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -223,6 +222,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "seg")) {
         if (value != 0 && (value < 8 || value > (1 << 20))) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
         h->opt_seg = (int)value;
+    } else if (!std::strcmp(key, "col_width")) {
+        if (value != 0 && value != 4 && value != 8) return msbfs_fail(MSBFS_ERR_INVALID, "col_width must be 0, 4 or 8");
+        h->opt_col_width = (int)value;
     } else if (!std::strcmp(key, "profile")) {
         h->opt_profile = value != 0;
     } else {
@@ -519,38 +521,31 @@ extern "C" int msbfs_get_level_log(msbfs_t* h, msbfs_level_record* out, int32_t 
     return MSBFS_OK;
 }
 
+extern "C" int msbfs_get_launch_log(msbfs_t* h, msbfs_launch_record* out, int32_t capacity, int32_t* count_out) {
+    if (!h || !count_out || capacity < 0 || (capacity > 0 && !out))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_launch_log: bad argument");
+    const int32_t total = (int32_t)h->launch_log.size();
+    const int32_t ncopy = total < capacity ? total : capacity;
+    if (ncopy > 0) std::memcpy(out, h->launch_log.data(), sizeof(msbfs_launch_record) * (size_t)ncopy);
+    *count_out = total;
+    return MSBFS_OK;
+}
+
+extern "C" int msbfs_get_batch_ms(msbfs_t* h, double* out, int32_t capacity, int32_t* count_out) {
+    if (!h || !count_out || capacity < 0 || (capacity > 0 && !out))
+        return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_batch_ms: bad argument");
+    const int32_t total = (int32_t)h->batch_ms.size();
+    const int32_t ncopy = total < capacity ? total : capacity;
+    if (ncopy > 0) std::memcpy(out, h->batch_ms.data(), sizeof(double) * (size_t)ncopy);
+    *count_out = total;
+    return MSBFS_OK;
+}
+
 extern "C" int msbfs_num_kernel_slots(void) { return MSBFS_NUM_SLOTS; }
 
 extern "C" int msbfs_get_kernel_profile(msbfs_t* h, int slot, msbfs_kernel_profile* out) {
     if (!h || !out || slot < 0 || slot >= MSBFS_NUM_SLOTS)
         return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_get_kernel_profile: bad argument");
     *out = h->slot_profile[slot];
-    return MSBFS_OK;
-}
-
-/* ------------------------------------------------------------- reduction --- */
-
-extern "C" int msbfs_allreduce_min_u64(msbfs_t* h, void* nccl_comm, uint64_t* inout) {
-    if (!h || !nccl_comm || !inout) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_allreduce_min_u64: null argument");
-    typedef int (*allreduce_fn)(const void*, void*, size_t, int, int, void*, cudaStream_t);
-    static allreduce_fn fn = nullptr;
-    if (!fn) {
-        void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD); /* reuse a copy the process already has */
-        if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW);
-        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW);
-        if (!lib) return msbfs_fail(MSBFS_ERR_INVALID, "NCCL not found: %s", dlerror());
-        fn = (allreduce_fn)dlsym(lib, "ncclAllReduce");
-        if (!fn) return msbfs_fail(MSBFS_ERR_INVALID, "ncclAllReduce not found in libnccl");
-    }
-    int rc = set_device(h);
-    if (rc) return rc;
-    if (!h->d_scalar) MSBFS_CUDA(cudaMalloc(&h->d_scalar, 8));
-    uint64_t* d = reinterpret_cast<uint64_t*>(h->d_scalar);
-    MSBFS_CUDA(cudaMemcpyAsync(d, inout, 8, cudaMemcpyHostToDevice, h->stream));
-    const int ncclUint64 = 5, ncclMin = 3; /* nccl.h: ncclDataType_t / ncclRedOp_t */
-    const int nrc = fn(d, d, 1, ncclUint64, ncclMin, nccl_comm, h->stream);
-    if (nrc != 0) return msbfs_fail(MSBFS_ERR_CUDA, "ncclAllReduce failed with code %d", nrc);
-    MSBFS_CUDA(cudaMemcpyAsync(inout, d, 8, cudaMemcpyDeviceToHost, h->stream));
-    MSBFS_CUDA(cudaStreamSynchronize(h->stream));
     return MSBFS_OK;
 }

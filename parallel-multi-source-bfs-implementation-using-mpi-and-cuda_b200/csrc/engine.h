@@ -180,6 +180,7 @@ struct msbfs_handle {
     int opt_reorder = 1;                       /* run groups heaviest-first (by their sources' degrees) */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
+    int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */
     long long opt_alpha = 40;
 
     /* stats of the last run */
@@ -188,6 +189,8 @@ struct msbfs_handle {
     int opt_profile = 0;                       /* time every kernel launch with CUDA events */
     std::vector<cudaEvent_t> ev_pool;          /* start/stop pairs, grown on demand         */
     msbfs_kernel_profile slot_profile[MSBFS_NUM_SLOTS]{};
+    std::vector<msbfs_launch_record> launch_log; /* one record per timed launch of the last run (option "profile") */
+    std::vector<double> batch_ms;              /* device time of every batch of the last run */
 };
 
 /* graph_build.cu */

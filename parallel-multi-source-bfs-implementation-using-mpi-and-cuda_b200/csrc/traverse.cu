@@ -47,7 +47,6 @@ namespace {
 typedef unsigned long long ull;
 
 constexpr int CTA = 256;
-constexpr int HUB_CTA = 512; /* bottom-up kernels with the hub bitmap in shared memory: one block per SM */
 #ifndef MSBFS_NW8_BLOCKS
 #define MSBFS_NW8_BLOCKS 2 /* resident 256-thread blocks per SM asked of the 512-lane bottom-up kernels */
 #endif
@@ -329,20 +328,12 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
  * every lane in `need` has been found. */
 template <int W> struct alignas(4 * W) ColVec { int v[W]; };
 
-/* W = col entries per load (4: one 128-bit load, 8: one 256-bit load).  HUB: the frontier
- * bitmap of the first a.hub_words * 32 vertices — the hubs, which is where most col entries
- * point — has been copied to shared memory by the block; a probe there costs a bank access
- * instead of one L1 wavefront per distinct 128-byte line (ncu r1/r2e: the four probe
- * instructions were half of the kernel's L1 wavefronts, 24 tag requests per instruction). */
-template <int NW, int W, bool HUB>
-__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, const unsigned* s_hub, long long beg, long long end,
+/* W = col entries per load (4: one 128-bit load, 8: one 256-bit load). */
+template <int NW, int W>
+__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, long long beg, long long end,
                                               const LW<NW>& need, unsigned& scanned, unsigned& fetched) {
     typedef ColVec<W> CV;
-    auto probe = [&](int v) -> unsigned {
-        const int w = v >> 5;
-        if (HUB && w < a.hub_words) return s_hub[w];
-        return a.cur_nz[w];
-    };
+    auto probe = [&](int v) -> unsigned { return a.cur_nz[v >> 5]; };
     LW<NW> acc = lw_zero<NW>();
     long long e = beg & ~(long long)(W - 1);
     CV c = *reinterpret_cast<const CV*>(a.col + e);
@@ -387,15 +378,6 @@ __device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, const unsigned*
     return acc;
 }
 
-/* the block's copy of the hub part of the frontier bitmap (dynamic shared memory) */
-extern __shared__ unsigned s_hub_bits[];
-template <bool HUB> __device__ __forceinline__ void load_hub_bits(const TravArgs& a) {
-    if (HUB) {
-        for (int i = threadIdx.x; i < a.hub_words; i += blockDim.x) s_hub_bits[i] = a.cur_nz[i];
-        __syncthreads();
-    }
-}
-
 /* The block's result bits: nxt_nz is fully rewritten every bottom-up level. */
 __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, int lane, unsigned fullw, unsigned nzbits,
                                                     unsigned fullbits) {
@@ -408,9 +390,8 @@ __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, in
 /* Rows of at most MSBFS_DEG_G8 entries: one thread per vertex, no cross-thread
  * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
  * each thread leaves its loop as soon as its own need is covered. */
-template <int NW, int W, bool HUB>
-__global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
-    load_hub_bits<HUB>(a);
+template <int NW, int W>
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     ull full_acc = 0;
@@ -427,7 +408,7 @@ __global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 :
             const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
             if (lw_any(need)) {
                 ++examined;
-                const LW<NW> acc = bu_scan_row<NW, W, HUB>(a, s_hub_bits, beg, end, need, scanned, fetched);
+                const LW<NW> acc = bu_scan_row<NW, W>(a, beg, end, need, scanned, fetched);
                 const LW<NW> found = lw_and(acc, need);
                 if (lw_any(found)) {
                     const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
@@ -453,9 +434,8 @@ __global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 :
  * and the early segments of a row have usually run before its later ones start.
  * Segments of a row co-operate through hub_acc: a segment first subtracts what earlier
  * segments already found and skips the row when nothing is left to find. */
-template <int NW, int W, bool HUB>
-__global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
-    load_hub_bits<HUB>(a);
+template <int NW, int W>
+__global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
@@ -480,7 +460,7 @@ __global__ void __launch_bounds__(HUB ? HUB_CTA : CTA, HUB ? 1 : (NW == 1) ? 6 :
         if (!lw_any(need)) continue;
         const long long beg = a.row_ptr[u] + (long long)k * a.seg;
         const long long end = min(beg + (long long)a.seg, a.row_ptr[u + 1]);
-        const LW<NW> acc = bu_scan_row<NW, W, HUB>(a, s_hub_bits, beg, end, need, scanned, fetched);
+        const LW<NW> acc = bu_scan_row<NW, W>(a, beg, end, need, scanned, fetched);
         const LW<NW> found = lw_and(acc, need);
         if (lw_any(found)) {
 #pragma unroll
@@ -1001,6 +981,9 @@ struct Launcher {
     long long launches = 0;
     int grid_cap;
     std::vector<int> pair_slot; /* slot of event pair i (events 2i, 2i+1 of h->ev_pool) */
+    std::vector<int> pair_batch, pair_level;
+    int cur_batch = 0, cur_level = -1;
+    std::vector<cudaEvent_t> batch_ev; /* start / stop of every batch */
 
     /* bracket one launch with CUDA events on the launching stream (option "profile") */
     template <class F> void timed(int slot, F&& launch) {
@@ -1020,15 +1003,35 @@ struct Launcher {
         if (rec) {
             cudaEventRecord(h->ev_pool[2 * i + 1], h->stream);
             pair_slot.push_back(slot);
+            pair_batch.push_back(cur_batch);
+            pair_level.push_back(cur_level);
         }
     }
+    void mark_batch() { /* called at the start and at the end of every batch */
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, h->stream);
+        batch_ev.push_back(e);
+    }
     void collect() {
+        h->launch_log.clear();
         for (size_t i = 0; i < pair_slot.size(); ++i) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, h->ev_pool[2 * i], h->ev_pool[2 * i + 1]) == cudaSuccess)
                 h->slot_profile[pair_slot[i]].ms += ms;
+            msbfs_launch_record r;
+            r.batch = pair_batch[i]; r.level = pair_level[i]; r.slot = pair_slot[i]; r.ms = ms;
+            h->launch_log.push_back(r);
         }
-        pair_slot.clear();
+        pair_slot.clear(); pair_batch.clear(); pair_level.clear();
+        h->batch_ms.clear();
+        for (size_t i = 0; i + 1 < batch_ev.size(); i += 2) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, batch_ev[i], batch_ev[i + 1]);
+            h->batch_ms.push_back((double)ms);
+        }
+        for (cudaEvent_t e : batch_ev) cudaEventDestroy(e);
+        batch_ev.clear();
     }
 
     int grid_for_warps(long long warps) const {
@@ -1059,6 +1062,14 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     a.seg_level_base = h->d_seg_level_base; a.n_seg_levels = h->n_seg_levels; a.n_seg_items = h->n_seg_items;
     a.seg = h->seg; a.blk_multi = h->blk_multi;
 
+    /* col entries per load: the long-row segments gain from 256-bit loads at 512 lanes (kron26
+     * bu_segment 26.2 -> 23.9 ms per step), the short rows of the thread kernel lose (85.2 -> 89.8:
+     * more masked work per row); "col_width" = 4 or 8 forces both */
+    const bool wide_seg = h->opt_col_width == 8 || (h->opt_col_width == 0 && NW == 8);
+    const bool wide = h->opt_col_width == 8;
+    void (*k_thread)(TravArgs, int, int) = wide ? bu_thread_kernel<NW, 8> : bu_thread_kernel<NW, 4>;
+    void (*k_segment)(TravArgs) = wide_seg ? bu_segment_kernel<NW, 8> : bu_segment_kernel<NW, 4>;
+
     /* persistent top-down kernel: only when every row is short and the device can co-schedule the grid */
     int streak_grid = 0;
     if (h->opt_streak && h->max_degree <= (unsigned)h->opt_streak_max_deg) {
@@ -1080,6 +1091,8 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
     for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
         const int lanes = std::min(lanes_per_batch, K - group_base);
+        L.cur_batch = batches; L.cur_level = -1;
+        L.mark_batch();
         L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz, (long long)h->n_active); });
         MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
         MSBFS_CUDA(cudaMemsetAsync(h->d_bitmaps, 0, sizeof(unsigned) * 3 * (size_t)nblk, s));
@@ -1105,6 +1118,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             const int dir = h->h_verdict->next_direction;
             const bool heavy_frontier = h->h_verdict->heavy_frontier != 0;
             ++levels;
+            ++L.cur_level;
             if (dir == 1 && streak_grid > 0) {
                 /* short-row graph: stay on the device for as many top-down levels as it takes */
                 MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
@@ -1119,6 +1133,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                 MSBFS_CUDA(cudaStreamSynchronize(s));
                 const int run = h->h_verdict->streak_levels;
                 levels += run - 1;
+                L.cur_level += run - 1;
                 levels_td += run;
                 /* the kernel swapped the frontier buffers `run` times; the loop head swaps once more */
                 if (run % 2 == 0) { std::swap(a.cur, a.nxt); std::swap(a.cur_nz, a.nxt_nz); }
@@ -1147,7 +1162,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                 if (a.blk_multi > 0) {
                     if (a.n_seg_items > 0)
                         L.timed(SLOT_BU_HEAVY, [&] {
-                            bu_segment_kernel<NW, 4><<<L.grid_for_warps((a.n_seg_items + 31) / 32), CTA, 0, s>>>(a);
+                            k_segment<<<L.grid_for_warps((a.n_seg_items + 31) / 32), CTA, 0, s>>>(a);
                         });
                     L.timed(SLOT_BU_HEAVY_FINALIZE, [&] {
                         bu_heavy_finalize_kernel<NW><<<L.grid_for_warps(a.blk_multi), CTA, 0, s>>>(a, a.blk_multi);
@@ -1155,7 +1170,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                 }
                 if (a.blk_end > a.blk_multi)
                     L.timed(SLOT_BU_G2, [&] {
-                        bu_thread_kernel<NW, 4><<<L.grid_for_warps(a.blk_end - a.blk_multi), CTA, 0, s>>>(a, a.blk_multi, a.blk_end);
+                        k_thread<<<L.grid_for_warps(a.blk_end - a.blk_multi), CTA, 0, s>>>(a, a.blk_multi, a.blk_end);
                     });
             }
             L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
@@ -1166,6 +1181,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             MSBFS_CUDA(cudaGetLastError());
         }
         L.timed(SLOT_OTHER, [&] { store_sums_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_sums, group_base, lanes); });
+        L.mark_batch();
 
         if (want_reached) {
             MSBFS_CUDA(cudaMemsetAsync(d_reached, 0, sizeof(ull) * MSBFS_MAX_LANES, s));

@@ -13,7 +13,8 @@
  *   - groups are ordered by their sources' degrees and handed to the ranks in contiguous runs of
  *     512-lane batches instead of round-robin single queries (main.cu:303-307);
  *   - the (q, F) Pair gather + scatter + two-pass argmin (main.cu:324-397) becomes one
- *     8-byte unsigned-min all-reduce of (F << 24 | q).
+ *     8-byte unsigned-min all-reduce of (F << 24 | q): over NCCL when every rank has its own
+ *     GPU (np <= gn), over MPI when ranks share one.
  * Opt-in extras that leave the default output untouched:
  *   --dump-sums <file>   gather every F on rank 0 and write "k F" lines
  *   MSBFS_STATS=1        traversal counters on stderr
@@ -96,6 +97,27 @@ int main(int argc, char* argv[]) {
     int64_t m = 0;
     if (msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
 
+    /* Result reduction over NCCL / NVLink when every rank has a GPU of its own (np <= gn):
+     * rank 0's ncclUniqueId travels by MPI_Bcast.  With ranks sharing a device (np > gn) NCCL
+     * cannot form a communicator and MPI carries the 8 bytes.  The communicator is set up
+     * inside the preprocessing window (the reference sets up its Pair datatype in the
+     * computation window, main.cu:326-328; this is the dearer of the two places to charge it).
+     * MSBFS_NO_NCCL=1 forces the MPI path. */
+    void* nccl_comm = nullptr;
+    if (world_size > 1 && world_size <= numGPU && !getenv("MSBFS_NO_NCCL")) {
+        unsigned char id[MSBFS_NCCL_ID_BYTES];
+        int ok = 1;
+        if (world_rank == 0 && msbfs_nccl_unique_id(id) != MSBFS_OK) ok = 0;
+        MPI_Bcast(&ok, 1, MPI_INT, 0, MPI_COMM_WORLD);
+        if (ok) {
+            MPI_Bcast(id, MSBFS_NCCL_ID_BYTES, MPI_BYTE, 0, MPI_COMM_WORLD);
+            if (msbfs_nccl_comm_create(eng, id, world_size, world_rank, &nccl_comm) != MSBFS_OK) die(world_rank, "NCCL communicator");
+        } else if (world_rank == 0) {
+            fprintf(stderr, "NCCL unavailable (%s): reducing over MPI\n", msbfs_last_error());
+        }
+    }
+
+
     /* every rank ready before the clock stops, as the reference's broadcasts imply */
     MPI_Barrier(MPI_COMM_WORLD);
     auto end_preprocessing = chrono::high_resolution_clock::now();
@@ -109,32 +131,19 @@ int main(int argc, char* argv[]) {
      * their levels together, so the bottom-up kernels can stop early for the whole batch.  Every
      * rank computes the same order from the same inputs; no communication is needed. */
     vector<int32_t> my_ids;
-    int batch_lanes = 0; /* 0 = the engine's own choice */
+    int32_t batch_lanes = 0; /* 0 = the engine's own choice */
     {
         vector<int64_t> cost((size_t)max(K, 1), 0);
         if (K > 0 && msbfs_group_weights(eng, K, q_offsets, q_sources, cost.data()) != MSBFS_OK)
             die(world_rank, "msbfs_group_weights");
-        vector<int32_t> order((size_t)K);
-        for (int32_t g = 0; g < K; ++g) order[(size_t)g] = g;
-        stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) { return cost[(size_t)x] > cost[(size_t)y]; });
-        /* batches of 512 groups of that order (256 when a rank would get fewer than two, less when
-         * there are fewer batches than ranks), handed out in snake order 0..R-1, R-1..0, ... so that
-         * every rank gets fast and slow batches */
-        if (world_size > 1) {
-            batch_lanes = 512;
-            if (((int64_t)K + batch_lanes - 1) / batch_lanes < 2 * (int64_t)world_size) batch_lanes = 256;
-            while (batch_lanes > 64 && ((int64_t)K + batch_lanes - 1) / batch_lanes < world_size) batch_lanes /= 2;
-            const int64_t nb = ((int64_t)K + batch_lanes - 1) / batch_lanes;
-            for (int64_t b = 0; b < nb; ++b) {
-                const int64_t lap = b / world_size, pos = b % world_size;
-                const int64_t owner = (lap % 2 == 0) ? pos : world_size - 1 - pos;
-                if (owner != world_rank) continue;
-                const int64_t lo = b * batch_lanes, hi = min<int64_t>(lo + batch_lanes, K);
-                my_ids.insert(my_ids.end(), order.begin() + lo, order.begin() + hi);
-            }
-        } else {
-            my_ids = order;
-        }
+        /* msbfs_plan_shares: batches of 512 groups of that order (256 when a rank would get fewer
+         * than two, less when there are fewer batches than ranks), handed out in snake order
+         * 0..R-1, R-1..0, ... so that every rank gets fast and slow batches */
+        vector<int32_t> order((size_t)max(K, 1)), owner((size_t)max(K, 1));
+        if (msbfs_plan_shares(K, cost.data(), world_size, 0, nullptr, 0, order.data(), owner.data(), &batch_lanes) != MSBFS_OK)
+            die(world_rank, "msbfs_plan_shares");
+        for (int32_t i = 0; i < K; ++i)
+            if (owner[(size_t)order[(size_t)i]] == world_rank) my_ids.push_back(order[(size_t)i]);
     }
     if (batch_lanes && msbfs_set_option(eng, "lanes", batch_lanes) != MSBFS_OK) die(world_rank, "lanes");
     const int32_t mine = (int32_t)my_ids.size();
@@ -156,21 +165,29 @@ int main(int argc, char* argv[]) {
     int32_t minK = -1;
     int64_t minF = -1; /* K = 0 keeps (-1, -1), main.cu:379-380 */
     uint64_t packed = UINT64_MAX;
-    int packable = msbfs_argmin_packed_ids(local_F.data(), my_ids.data(), mine, &packed) == MSBFS_OK ? 1 : 0;
-    MPI_Allreduce(MPI_IN_PLACE, &packable, 1, MPI_INT, MPI_MIN, MPI_COMM_WORLD);
+    /* 8-byte unsigned min over all ranks: NCCL when there is a communicator, else MPI */
+    auto min_u64 = [&](unsigned long long v) -> unsigned long long {
+        if (nccl_comm) {
+            uint64_t w = v;
+            if (msbfs_allreduce_min_u64(eng, nccl_comm, &w) != MSBFS_OK) die(world_rank, "msbfs_allreduce_min_u64");
+            return w;
+        }
+        MPI_Allreduce(MPI_IN_PLACE, &v, 1, MPI_UNSIGNED_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
+        return v;
+    };
+    const bool packable_here = msbfs_argmin_packed_ids(local_F.data(), my_ids.data(), mine, &packed) == MSBFS_OK;
+    const bool packable = min_u64(packable_here ? 1ull : 0ull) == 1ull;
     if (packable) {
-        unsigned long long best = packed;
-        MPI_Allreduce(MPI_IN_PLACE, &best, 1, MPI_UNSIGNED_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
-        msbfs_unpack_argmin((uint64_t)best, &minK, &minF);
+        msbfs_unpack_argmin((uint64_t)min_u64(packed), &minK, &minF);
     } else {
-        long long gf = INT64_MAX;
-        for (int32_t p = 0; p < mine; ++p) gf = min<long long>(gf, local_F[(size_t)p]);
-        MPI_Allreduce(MPI_IN_PLACE, &gf, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
-        long long gk = INT64_MAX;
+        unsigned long long gf = UINT64_MAX; /* sums are non-negative: unsigned order = signed order */
+        for (int32_t p = 0; p < mine; ++p) gf = min<unsigned long long>(gf, (unsigned long long)local_F[(size_t)p]);
+        gf = min_u64(gf);
+        unsigned long long gk = UINT64_MAX;
         for (int32_t p = 0; p < mine; ++p)
-            if (local_F[(size_t)p] == gf) gk = min<long long>(gk, my_ids[(size_t)p]);
-        MPI_Allreduce(MPI_IN_PLACE, &gk, 1, MPI_LONG_LONG, MPI_MIN, MPI_COMM_WORLD);
-        if (gk != INT64_MAX) { minK = (int32_t)gk; minF = gf; }
+            if ((unsigned long long)local_F[(size_t)p] == gf) gk = min<unsigned long long>(gk, (unsigned long long)my_ids[(size_t)p]);
+        gk = min_u64(gk);
+        if (gk != UINT64_MAX) { minK = (int32_t)gk; minF = (int64_t)gf; }
     }
 
     auto end_computation = chrono::high_resolution_clock::now();
@@ -215,12 +232,13 @@ int main(int argc, char* argv[]) {
         if (msbfs_get_stats(eng, &st) == MSBFS_OK)
             fprintf(stderr,
                     "[rank %d] groups=%d lanes=%d batches=%d levels=%lld (td %lld, bu %lld) scanned td=%lld bu=%lld "
-                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f\n",
+                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f reduce=%s\n",
                     world_rank, mine, st.lanes, st.batches, (long long)st.levels, (long long)st.levels_top_down,
                     (long long)st.levels_bottom_up, (long long)st.scanned_top_down, (long long)st.scanned_bottom_up,
-                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms);
+                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms, nccl_comm ? "nccl" : "mpi");
     }
 
+    msbfs_nccl_comm_destroy(nccl_comm);
     msbfs_destroy(eng); /* main.cu:416-418 */
     msbfs_free(q_offsets);
     msbfs_free(q_sources);

@@ -171,6 +171,17 @@ def test_share_planning_and_explicit_id_packing(pkg, ob):
         sums = rng.integers(0, 6, size=k).astype(np.int64)
         packed = [pkg.argmin_packed_ids(sums[sh], sh) for sh in share]
         assert pkg.unpack_argmin(min(packed)) == ob.argmin(sums)
+    # planning from measured batch cost: longest batch first onto the least-loaded rank
+    costs = np.arange(4096, 0, -1).astype(np.int64)           # run order = file order
+    measured = np.array([13, 14, 15, 16, 18, 20, 23, 26.6] * 2)  # 16 batches of 256
+    share, lanes = pkg.plan_shares(costs, 8, lanes=256, batch_cost=measured)
+    assert lanes == 256 and sorted(np.concatenate(share).tolist()) == list(range(4096))
+    loads = [sum(measured[g // 256] for g in sh[::256].tolist()) for sh in share]
+    snake, _ = pkg.plan_shares(costs, 8, lanes=256)
+    loads_snake = [sum(measured[g // 256] for g in sh[::256].tolist()) for sh in snake]
+    assert max(loads) <= max(loads_snake) and max(loads) < 1.15 * sum(measured) / 8
+    assert pkg.lib().msbfs_plan_lanes(4096, 1) == 0 and pkg.lib().msbfs_plan_lanes(4096, 8) == 256
+    assert pkg.lib().msbfs_plan_lanes(4096, 2) == 512 and pkg.lib().msbfs_plan_lanes(100, 8) == 64
     offs = np.array([0, 2, 2, 5, 6], dtype=np.int64)
     src = np.arange(6, dtype=np.int32)
     o2, s2 = pkg.gather_groups(offs, src, np.array([2, 0, 1]))
