@@ -59,6 +59,8 @@ int msbfs_destroy(msbfs_t* h);
  *   "reorder"    1 = run the groups heaviest-first (sum of their sources' degrees) so that groups
  *                with hubs among their sources share batches (default), 0 = caller's order
  *   "profile"    1 = time every kernel launch with CUDA events (msbfs_get_kernel_profile)
+ *   "expect_groups"  most groups a run on this handle will carry (0 = unknown): the traversal
+ *                state allocated at graph load is sized for it instead of for 512 lanes
  *   "col_width"  col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the
  *                long-row kernel of 512-lane batches and 4 elsewhere (default)
  * Layout knobs read at the next graph load (defaults chosen by sweeps):
@@ -85,6 +87,17 @@ int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int32_t* uv_pa
 /* Same, from records already resident in this handle's device memory
  * (e.g. produced by msbfs_gen_edges_device). The buffer is only read. */
 int msbfs_set_graph_edges_device(msbfs_t* h, int32_t n, int64_t m, const int32_t* d_uv_pairs);
+
+/* One CSR per GPU for ranks that share it (replaces the per-rank cudaMalloc + upload of
+ * main.cu:283-291 when `mpirun -np R ... -gn G` puts R / G ranks on a device, main.cu:227).
+ * The rank that loaded the graph exports a blob — sizes, layout tables and CUDA IPC handles
+ * of the CSR arrays; call with capacity 0 to learn its size — the host program ships the
+ * bytes to the other ranks on that device (MPI_Bcast in host/main.cpp), and each of them
+ * imports it into its own handle, which then reads the exporter's arrays.  The exporter's
+ * handle must outlive every importer's.  Import fails with MSBFS_ERR_CUDA where CUDA IPC is
+ * not available (load the file instead) and refuses a blob made for another device. */
+int msbfs_export_graph(msbfs_t* h, void* blob, int64_t capacity, int64_t* size_out);
+int msbfs_import_graph(msbfs_t* h, const void* blob, int64_t size);
 
 /* --------------------------------------------------------------- queries -- */
 

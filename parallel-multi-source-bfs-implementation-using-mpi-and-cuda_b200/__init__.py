@@ -94,6 +94,8 @@ SIGNATURES = {
     "msbfs_load_graph_file": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "msbfs_set_graph_edges": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]),
     "msbfs_set_graph_edges_device": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]),
+    "msbfs_export_graph": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "msbfs_import_graph": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "msbfs_run": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "msbfs_upload_queries": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "msbfs_run_resident": (C.c_int, [C.c_void_p]),

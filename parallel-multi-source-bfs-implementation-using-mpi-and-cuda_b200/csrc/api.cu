@@ -28,21 +28,36 @@ constexpr int STAGE_THREADS = 4;          /* filler threads, two buffers each */
  * keep PCIe busy.  The buffers live in the handle and are allocated once.
  * Replaces the per-field fread loop and the pageable blocking cudaMemcpy of the reference
  * (main.cu:108-116, 290-291).  fill(dst, offset, len) returns 0 or an errno-style code. */
-int ensure_stage(msbfs_handle* h) {
-    for (int i = 0; i < 2 * STAGE_THREADS; ++i) {
-        if (!h->stage_buf[i]) MSBFS_CUDA(cudaHostAlloc((void**)&h->stage_buf[i], STAGE_BYTES, cudaHostAllocDefault));
-        if (!h->stage_ev[i]) MSBFS_CUDA(cudaEventCreateWithFlags(&h->stage_ev[i], cudaEventDisableTiming));
+int ensure_stage(msbfs_handle* h, int slot, size_t bytes) {
+    if (h->stage_buf[slot] && h->stage_cap[slot] < bytes) {
+        cudaFreeHost(h->stage_buf[slot]);
+        h->stage_buf[slot] = nullptr;
+        h->stage_cap[slot] = 0;
     }
+    if (!h->stage_buf[slot]) {
+        MSBFS_CUDA(cudaHostAlloc((void**)&h->stage_buf[slot], bytes, cudaHostAllocDefault));
+        h->stage_cap[slot] = bytes;
+    }
+    if (!h->stage_ev[slot]) MSBFS_CUDA(cudaEventCreateWithFlags(&h->stage_ev[slot], cudaEventDisableTiming));
     return MSBFS_OK;
 }
 
 template <class Fill>
 int staged_upload(msbfs_handle* h, char* d_dst, size_t total, Fill fill, const char* what) {
     if (total == 0) return MSBFS_OK;
-    int rc = ensure_stage(h);
-    if (rc) return rc;
     const size_t nchunks = (total + STAGE_BYTES - 1) / STAGE_BYTES;
     const int nthreads = (int)std::min<size_t>(STAGE_THREADS, nchunks);
+    /* only the buffers this upload will use, and no larger than it needs: pinning memory costs
+     * milliseconds per buffer, which is most of the preprocessing window of a small graph */
+    const size_t one = nchunks == 1 ? ((total + 4095) / 4096) * 4096 : STAGE_BYTES;
+    for (int t = 0; t < nthreads; ++t) {
+        int rc = ensure_stage(h, 2 * t, one);
+        if (rc) return rc;
+        if (nchunks > (size_t)(t + nthreads)) { /* this thread gets a second chunk: double-buffer */
+            rc = ensure_stage(h, 2 * t + 1, one);
+            if (rc) return rc;
+        }
+    }
     std::atomic<int> failed{0};
     std::atomic<int> cuda_err{0};
     auto worker = [&](int t) {
@@ -222,6 +237,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "seg")) {
         if (value != 0 && (value < 8 || value > (1 << 20))) return msbfs_fail(MSBFS_ERR_INVALID, "seg out of range");
         h->opt_seg = (int)value;
+    } else if (!std::strcmp(key, "expect_groups")) {
+        if (value < 0) return msbfs_fail(MSBFS_ERR_INVALID, "expect_groups must be >= 0");
+        h->opt_expect_groups = (int)std::min<int64_t>(value, 1 << 30);
     } else if (!std::strcmp(key, "col_width")) {
         if (value != 0 && value != 4 && value != 8) return msbfs_fail(MSBFS_ERR_INVALID, "col_width must be 0, 4 or 8");
         h->opt_col_width = (int)value;

@@ -140,6 +140,7 @@ struct msbfs_handle {
     int n_seg_levels = 0, blk_multi = 0, seg = 256;
     long long n_seg_items = 0;
     bool has_graph = false;
+    bool graph_imported = false;  /* perm / row_ptr / col belong to another process (share.cu): close, do not free */
     unsigned max_degree = 0;
     double build_ms = 0.0;
 
@@ -170,6 +171,7 @@ struct msbfs_handle {
 
     /* pinned staging buffers of the loader (api.cu), allocated on first use */
     char* stage_buf[8] = {};
+    size_t stage_cap[8] = {};
     cudaEvent_t stage_ev[8] = {};
 
     /* options */
@@ -179,6 +181,7 @@ struct msbfs_handle {
     int opt_streak_max_deg = 256;              /* longest row for which the persistent kernel is used */
     int opt_reorder = 1;                       /* run groups heaviest-first (by their sources' degrees) */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
+    int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */
     long long opt_alpha = 40;

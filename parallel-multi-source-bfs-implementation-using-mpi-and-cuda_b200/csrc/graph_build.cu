@@ -125,9 +125,18 @@ inline int grid_for(long long items, int threads, int sm_count) {
 } // namespace
 
 void msbfs_release_graph(msbfs_handle* h) {
-    cudaFree(h->d_perm); h->d_perm = nullptr;
-    cudaFree(h->d_row_ptr); h->d_row_ptr = nullptr;
-    cudaFree(h->d_col); h->d_col = nullptr;
+    if (h->graph_imported) { /* mapped from the owning process: unmap */
+        if (h->d_perm) cudaIpcCloseMemHandle(h->d_perm);
+        if (h->d_row_ptr) cudaIpcCloseMemHandle(h->d_row_ptr);
+        if (h->d_col) cudaIpcCloseMemHandle(h->d_col);
+        cudaGetLastError();
+    } else {
+        cudaFree(h->d_perm);
+        cudaFree(h->d_row_ptr);
+        cudaFree(h->d_col);
+    }
+    h->graph_imported = false;
+    h->d_perm = nullptr; h->d_row_ptr = nullptr; h->d_col = nullptr;
     cudaFree(h->d_chunk_level_base); h->d_chunk_level_base = nullptr;
     cudaFree(h->d_seg_level_base); h->d_seg_level_base = nullptr;
     h->has_graph = false;

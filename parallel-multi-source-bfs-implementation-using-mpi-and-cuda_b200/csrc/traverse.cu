@@ -1383,9 +1383,13 @@ void msbfs_prealloc_traversal(msbfs_handle* h) {
     if (!h->has_graph || h->n_active == 0) return;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return; }
-    const size_t need = (size_t)h->n_pad * MSBFS_MAX_NW * sizeof(ull) * 4 + (size_t)h->blk_multi * 32 * MSBFS_MAX_NW * sizeof(ull);
+    /* the widest word, unless the caller has said how many groups its runs will carry */
+    int nw = MSBFS_MAX_NW;
+    if (h->opt_lanes) nw = h->opt_lanes / 64;
+    else if (h->opt_expect_groups > 0) nw = h->opt_expect_groups <= 64 ? 1 : h->opt_expect_groups <= 128 ? 2 : h->opt_expect_groups <= 256 ? 4 : 8;
+    const size_t need = (size_t)h->n_pad * nw * sizeof(ull) * 4 + (size_t)h->blk_multi * 32 * nw * sizeof(ull);
     if (need + (need >> 1) > free_b) return;
-    if (ensure_traversal_buffers(h, MSBFS_MAX_NW) != MSBFS_OK) {
+    if (ensure_traversal_buffers(h, nw) != MSBFS_OK) {
         cudaGetLastError();
         msbfs_release_traversal(h);
         msbfs_clear_error();

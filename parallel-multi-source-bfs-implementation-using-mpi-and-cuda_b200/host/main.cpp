@@ -7,8 +7,9 @@
  *   mpirun -np <ranks> ./main -g <graph.bin> -q <query.bin> -gn <numGPU>
  *
  * What changed underneath:
- *   - every rank loads the graph itself through the pinned/async loader and builds
- *     the CSR on its GPU (no host CSR, no MPI_Bcast of up to 8 GiB, main.cu:237-255);
+ *   - one rank per GPU loads the graph through the pinned/async loader and builds the CSR on
+ *     the device (no host CSR, no MPI_Bcast of up to 8 GiB, main.cu:237-255); ranks that share
+ *     a GPU map that CSR through CUDA IPC instead of uploading their own (main.cu:283-291);
  *   - queries are read by every rank (a few KB; replaces 2K broadcasts, main.cu:264-280);
  *   - groups are ordered by their sources' degrees and handed to the ranks in contiguous runs of
  *     512-lane batches instead of round-robin single queries (main.cu:303-307);
@@ -64,10 +65,6 @@ int main(int argc, char* argv[]) {
     }
     if (numGPU < 1) numGPU = 1; /* the reference divides by zero here (main.cu:227) */
     const int device_id = world_rank % numGPU; /* main.cu:227 */
-
-    /* ---- preprocessing window (main.cu:235 -> 297) -------------------------- */
-    auto start_preprocessing = chrono::high_resolution_clock::now();
-
     /* The reference opens the graph, then the query file, on rank 0 and exits with
      * status 1 when either is missing (main.cu:94-99, 137-141) while its peers wait in
      * MPI_Bcast until mpirun tears the job down.  Same here, checked before the GPU is
@@ -85,17 +82,58 @@ int main(int argc, char* argv[]) {
     require_file(graphFile, "graph");
     require_file(queryFile, "query");
 
+    /* main.cu:228 — cudaSetDevice, before the preprocessing clock starts (CUDA 12 creates the
+     * context there); msbfs_create is its replacement and sits at the same place */
+    msbfs_t* eng = nullptr;
+    if (msbfs_create(device_id, &eng) != MSBFS_OK) die(world_rank, "msbfs_create");
+
+    /* ---- preprocessing window (main.cu:235 -> 297) -------------------------- */
+    auto start_preprocessing = chrono::high_resolution_clock::now();
+
     int32_t K = 0;
     int64_t* q_offsets = nullptr;
     int32_t* q_sources = nullptr;
     /* main.cu:134-164 (every rank reads the small file instead of 2K broadcasts) */
     if (msbfs_load_query_file(queryFile.c_str(), &K, &q_offsets, &q_sources) != MSBFS_OK) die(world_rank, "query file");
 
-    msbfs_t* eng = nullptr;
-    if (msbfs_create(device_id, &eng) != MSBFS_OK) die(world_rank, "msbfs_create");
+    /* the traversal state is sized at graph load: say how wide this rank's batches will be */
+    {
+        const int lanes = msbfs_plan_lanes(K, world_size);
+        if (lanes > 0) msbfs_set_option(eng, "lanes", lanes);
+        else msbfs_set_option(eng, "expect_groups", K);
+    }
     int32_t n = 0;
     int64_t m = 0;
-    if (msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
+    /* One CSR per GPU (replaces the per-rank upload of main.cu:283-291): the lowest rank on a
+     * device loads the file and builds the CSR; ranks that share its device (np > gn) map the
+     * same arrays through CUDA IPC.  MSBFS_NO_IPC=1 makes every rank load for itself. */
+    const bool share = world_size > numGPU && !getenv("MSBFS_NO_IPC");
+    const bool owner = !share || world_rank < numGPU;
+    bool graph_shared = false;
+    if (owner && msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
+    if (share) {
+        for (int d = 0; d < numGPU; ++d) { /* rank d owns device d */
+            long long size = 0;
+            vector<unsigned char> blob;
+            if (world_rank == d) {
+                int64_t sz = 0;
+                if (msbfs_export_graph(eng, nullptr, 0, &sz) != MSBFS_OK) die(world_rank, "msbfs_export_graph");
+                blob.resize((size_t)sz);
+                if (msbfs_export_graph(eng, blob.data(), sz, &sz) != MSBFS_OK) die(world_rank, "msbfs_export_graph");
+                size = sz;
+            }
+            MPI_Bcast(&size, 1, MPI_LONG_LONG, d, MPI_COMM_WORLD);
+            blob.resize((size_t)size);
+            MPI_Bcast(blob.data(), (int)size, MPI_BYTE, d, MPI_COMM_WORLD);
+            if (world_rank != d && device_id == d) {
+                if (msbfs_import_graph(eng, blob.data(), size) == MSBFS_OK) graph_shared = true;
+                else { /* e.g. IPC not permitted in this container: fall back to an own copy */
+                    if (getenv("MSBFS_STATS")) fprintf(stderr, "[rank %d] %s; loading an own copy\n", world_rank, msbfs_last_error());
+                    if (msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
+                }
+            }
+        }
+    }
 
     /* Result reduction over NCCL / NVLink when every rank has a GPU of its own (np <= gn):
      * rank 0's ncclUniqueId travels by MPI_Bcast.  With ranks sharing a device (np > gn) NCCL
@@ -232,13 +270,17 @@ int main(int argc, char* argv[]) {
         if (msbfs_get_stats(eng, &st) == MSBFS_OK)
             fprintf(stderr,
                     "[rank %d] groups=%d lanes=%d batches=%d levels=%lld (td %lld, bu %lld) scanned td=%lld bu=%lld "
-                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f reduce=%s\n",
+                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f reduce=%s graph=%s\n",
                     world_rank, mine, st.lanes, st.batches, (long long)st.levels, (long long)st.levels_top_down,
                     (long long)st.levels_bottom_up, (long long)st.scanned_top_down, (long long)st.scanned_bottom_up,
-                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms, nccl_comm ? "nccl" : "mpi");
+                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms, nccl_comm ? "nccl" : "mpi", graph_shared ? "shared" : "own");
     }
 
     msbfs_nccl_comm_destroy(nccl_comm);
+    if (share) { /* an owner keeps its arrays until the ranks that map them are done */
+        if (!owner) { msbfs_destroy(eng); eng = nullptr; }
+        MPI_Barrier(MPI_COMM_WORLD);
+    }
     msbfs_destroy(eng); /* main.cu:416-418 */
     msbfs_free(q_offsets);
     msbfs_free(q_sources);

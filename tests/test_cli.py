@@ -72,3 +72,58 @@ def test_report_matches_reference(pkg, ob, expected, tmp_path, name, ranks):
     assert res.stdout.splitlines()[2:5] == expected[name]["report_lines_3_to_5"]
     got = [int(line.split()[1]) for line in open(dump)] if os.path.exists(dump) else []
     assert got == expected[name]["sums"]
+
+
+@pytest.mark.gpu
+def test_ranks_on_one_gpu_share_one_csr(pkg, ob, expected, tmp_path):
+    """`mpirun -np 3 ... -gn 1` (ranks > GPUs, main.cu:227): rank 0 builds the CSR, ranks 1 and 2
+    map it through CUDA IPC (msbfs_export_graph / msbfs_import_graph) instead of uploading
+    their own copies as the reference does (main.cu:283-291); MSBFS_NO_IPC=1 keeps one copy per
+    rank.  Same report either way."""
+    main, mpirun = _paths(pkg)
+    name = "rmat16_64x4"
+    n, uv, offs, src = golden_case_inputs(pkg, ob, expected, name)
+    gpath = str(tmp_path / "g.bin")
+    qpath = os.path.join(os.path.dirname(__file__), "golden", expected[name]["query_file"])
+    pkg.write_graph_file(gpath, n, uv)
+    outs = {}
+    for no_ipc in (False, True):
+        env = dict(os.environ, MSBFS_STATS="1")
+        if no_ipc:
+            env["MSBFS_NO_IPC"] = "1"
+        res = subprocess.run([mpirun, "-np", "3", main, "-g", gpath, "-q", qpath, "-gn", "1"], capture_output=True, text=True,
+                             timeout=300, env=env)
+        assert res.returncode == 0, res.stderr
+        m = REPORT.match(res.stdout)
+        assert m, res.stdout
+        assert int(m["k"]) == expected[name]["k_printed"] and int(m["f"]) == expected[name]["min_f"]
+        outs[no_ipc] = res.stderr
+    shared = [ln for ln in outs[False].splitlines() if "graph=" in ln]
+    assert len(shared) == 3 and sum("graph=shared" in ln for ln in shared) == 2, outs[False]
+    assert all("graph=own" in ln for ln in outs[True].splitlines() if "graph=" in ln)
+
+
+@pytest.mark.gpu
+def test_nccl_reduce_in_the_drop_in_two_gpus(pkg, ob, expected, tmp_path):
+    """`mpirun -np 2 ... -gn 2`: the packed-min reduction runs over NCCL (communicator made from
+    an ncclUniqueId broadcast over MPI); MSBFS_NO_NCCL=1 keeps MPI.  Needs two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    main, mpirun = _paths(pkg)
+    name = "kron12_200x3"
+    n, uv, offs, src = golden_case_inputs(pkg, ob, expected, name)
+    gpath = str(tmp_path / "g.bin")
+    qpath = os.path.join(os.path.dirname(__file__), "golden", expected[name]["query_file"])
+    pkg.write_graph_file(gpath, n, uv)
+    for no_nccl in (False, True):
+        env = dict(os.environ, MSBFS_STATS="1")
+        if no_nccl:
+            env["MSBFS_NO_NCCL"] = "1"
+        res = subprocess.run([mpirun, "-np", "2", main, "-g", gpath, "-q", qpath, "-gn", "2"], capture_output=True, text=True,
+                             timeout=300, env=env)
+        assert res.returncode == 0, res.stderr
+        m = REPORT.match(res.stdout)
+        assert m and int(m["k"]) == expected[name]["k_printed"] and int(m["f"]) == expected[name]["min_f"], res.stdout
+        want = "reduce=mpi" if no_nccl else "reduce=nccl"
+        assert sum(want in ln for ln in res.stderr.splitlines()) == 2, res.stderr
