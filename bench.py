@@ -311,6 +311,56 @@ def make_edges_host(pkg, wl, kind):
     return pkg.gen_edges_host(kind, wl["p0"], wl["p1"], wl["m"], GRAPH_SEED)
 
 
+def reference_gpu_block(pkg, args, wl, n, uv_host, our_qps):
+    """The reference's own GPU program — unmodified main.cu built for sm_100a (oracle/_ref/main_gpu)
+    — on this box, on the same graph file and the first <= 255 groups (its query format's limit,
+    main.cu:143-152); its own "Computation time" line (main.cu:412-413).  A reported baseline."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
+
+    if not os.path.exists(ob.REF_GPU):
+        return {"unavailable": "oracle/_ref/main_gpu not built (needs /root/reference at build time)"}
+    if (wl["m"] > (1 << 26) or wl["per_group"] > 255) and not args.ref_gpu_force:
+        return {"unavailable": "the reference's loader (one fread + push_back per id, main.cu:108-116) needs minutes for "
+                               f"{wl['m']} records" + (" and its query format caps a group at 255 sources" if wl["per_group"] > 255 else "")
+                               + "; run with --ref-gpu-force to wait for it"}
+    groups = min(args.ref_groups, wl["groups"], 255)
+    per_group = min(wl["per_group"], 255)
+    offs, src = pkg.gen_queries_host(n, wl["groups"], wl["per_group"], QUERY_SEED)
+    sel = [src[offs[i]:offs[i] + per_group] for i in range(groups)]
+    offs2 = np.concatenate([[0], np.cumsum([len(x) for x in sel])]).astype(np.int64)
+    src2 = np.concatenate(sel).astype(np.int32)
+    tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    with tempfile.TemporaryDirectory(dir=tmpdir) as tmp:
+        g, q = os.path.join(tmp, "graph.bin"), os.path.join(tmp, "query.bin")
+        pkg.write_graph_file(g, n, uv_host)
+        pkg.write_query_file(q, offs2, src2)
+        mpirun = os.path.join(pkg.PKG_DIR, "host", "mpirun")
+        out = {}
+        for name, exe in (("reference", ob.REF_GPU), ("drop_in", os.path.join(pkg.PKG_DIR, "host", "main"))):
+            try:
+                res = subprocess.run([mpirun, "-np", "1", exe, "-g", g, "-q", q, "-gn", "1"], capture_output=True, text=True,
+                                     timeout=args.ref_gpu_timeout)
+            except subprocess.TimeoutExpired:
+                return {"unavailable": f"{name} did not finish within {args.ref_gpu_timeout:.0f} s"}
+            if res.returncode != 0:
+                return {"unavailable": f"{name} failed: {res.stderr[-200:]}"}
+            rec = {}
+            for ln in res.stdout.splitlines():
+                if ln.startswith("Query number"): rec["k_printed"] = int(ln.split(":")[1])
+                elif ln.startswith("Minimum F value"): rec["min_f"] = int(ln.split(":")[1])
+                elif ln.startswith("Preprocessing time"): rec["preprocessing_s"] = float(ln.split()[2])
+                elif ln.startswith("Computation time"): rec["computation_s"] = float(ln.split()[2])
+            out[name] = rec
+    r, d = out["reference"], out["drop_in"]
+    return {"program": "oracle/_ref/main_gpu = unmodified /root/reference/main.cu, nvcc sm_100a, mpirun -np 1 -gn 1",
+            "sample": f"first {groups} groups x {per_group} sources of the workload (reference query format)",
+            "reference": r, "drop_in_main_same_files": d,
+            "queries_per_sec": groups / r["computation_s"] if r.get("computation_s") else None,
+            "same_answer": (r.get("k_printed"), r.get("min_f")) == (d.get("k_printed"), d.get("min_f")),
+            "ours_over_reference_queries_per_sec": (our_qps / (groups / r["computation_s"])) if r.get("computation_s") else None}
+
+
 # ------------------------------------------------------------------------------ our arm
 
 def run_ours(args, wl, rank, local_rank, world):
@@ -427,6 +477,50 @@ def run_ours(args, wl, rank, local_rank, world):
         flush_buf.zero_()
         one_step_resident()
 
+    # ---- plan from measured cost: the warm-up's per-batch device times (every rank's, in global
+    #      batch order) go back into msbfs_plan_shares, which hands the batches out longest first
+    #      to the least-loaded rank instead of in snake order
+    plan_note = "one rank" if world == 1 else ("contiguous file order" if args.contiguous else "snake order")
+    if world > 1 and not args.contiguous and not args.no_replan:
+        mine_ms = eng.batch_ms() if hi > lo else []
+        all_ms = [None] * world
+        dist.all_gather_object(all_ms, mine_ms)
+        width = plan_lanes or 512
+        nb = (K + width - 1) // width
+        order_all = np.concatenate(share)  # not in run order; rebuild it from the plan
+        run_order = np.lexsort((np.arange(K), -np.asarray(costs, dtype=np.int64)))
+        owner_of_batch = []
+        owner = np.empty(K, np.int64)
+        for r in range(world):
+            owner[share[r]] = r
+        cost_b, seen = [], [0] * world
+        for b in range(nb):
+            r = int(owner[run_order[b * width]])
+            owner_of_batch.append(r)
+            cost_b.append(float(all_ms[r][seen[r]]) if seen[r] < len(all_ms[r]) else 0.0)
+            seen[r] += 1
+        share2, _ = pkg.plan_shares(costs, world, lanes=width, batch_cost=np.array(cost_b))
+        loads_old = [sum(c for c, o in zip(cost_b, owner_of_batch) if o == r) for r in range(world)]
+        owner2 = np.empty(K, np.int64)
+        for r in range(world):
+            owner2[share2[r]] = r
+        loads_new = [sum(c for b, c in enumerate(cost_b) if int(owner2[run_order[b * width]]) == r) for r in range(world)]
+        if max(loads_new) < 0.98 * max(loads_old):
+            share = share2
+            mine = share[rank].astype(np.int64)
+            my_offs, my_src = pkg.gather_groups(offs, src, mine)
+            lo, hi = 0, int(mine.size)
+            h2d_bytes = int(my_offs.nbytes + my_src.nbytes)
+            d2h_bytes = int(mine.size * 8)
+            eng.upload_queries(my_offs, my_src)
+            flush_buf.zero_()
+            one_step_resident()  # the new share's own warm-up
+            plan_note = (f"longest batch first onto the least-loaded rank, from the warm-up's per-batch times "
+                         f"(planned max per rank {max(loads_new):.1f} ms vs {max(loads_old):.1f} ms in snake order)")
+        else:
+            plan_note = f"snake order (measured-cost plan no better: {max(loads_new):.1f} vs {max(loads_old):.1f} ms)"
+        del order_all
+
     # ---- timed steps: device time (events) per step, max over ranks; wall as a cross-check
     sampler = ClockSampler(local_rank)
     sync_all()
@@ -451,6 +545,12 @@ def run_ours(args, wl, rank, local_rank, world):
     clocks = sampler.stop()
     device_ms = reduce_max(sum(step_ms))
     ms_per_step = device_ms / args.steps
+    per_rank_ms = [sum(step_ms) / args.steps]
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, per_rank_ms[0])
+        per_rank_ms = [float(x) for x in gathered]
+    batch_ms_rank0 = [round(x, 3) for x in eng.batch_ms()] if hi > lo else []
     stats = eng.stats() if hi > lo else {}
     min_k, min_f = pkg.unpack_argmin(best)
 
@@ -499,8 +599,12 @@ def run_ours(args, wl, rank, local_rank, world):
                     traffic = json.load(open(tpath)).get(args.workload, {}).get(top["name"])
                 except Exception:
                     traffic = None
+            avg_ms = top["ms"] / top["launches"]
             roofline = {"bound": "hbm", "kernel": top["name"], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                         "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                        "frac_note": "achieved = ALGORITHMIC bytes / time (SURVEY 8(d)); dram_frac = ncu DRAM bytes per launch "
+                                     "(traffic, profiles/traffic.json) / the same time: hub words are served from L2",
+                        "dram_frac": round(traffic / 1e9 / (avg_ms / 1e3) / peak, 4) if traffic else None,
                         "alg_bytes_per_launch": int(top["alg_bytes"] / top["launches"]),
                         "avg_launch_ms": round(top["ms"] / top["launches"], 4),
                         "whole_step": {"alg_bytes": int(stats.get("alg_bytes", 0)),
@@ -530,6 +634,16 @@ def run_ours(args, wl, rank, local_rank, world):
         if not ok:
             log("PARITY FAILURE against the oracle on the sampled groups")
 
+    ref_gpu = None
+    if want_cpu:
+        try:
+            ref_gpu = reference_gpu_block(pkg, args, wl, n, uv_host, K / (ms_per_step / 1e3))
+        except Exception as e:  # a reported baseline must not take the bench line down
+            ref_gpu = {"unavailable": f"{type(e).__name__}: {e}"}
+        if ref_gpu and ref_gpu.get("same_answer") is False:
+            log("PARITY FAILURE: the drop-in and the reference's GPU build disagree on the same files")
+            parity = dict(parity or {}, bit_exact=False)
+
     value = traversed_edges_total / (ms_per_step / 1e3) / 1e9
     line = {
         "metric": "GTEPS", "value": value, "unit": "GTEPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -538,7 +652,7 @@ def run_ours(args, wl, rank, local_rank, world):
         "config": {"workload": args.workload, "description": wl["desc"], "graph_seed": GRAPH_SEED, "query_seed": QUERY_SEED,
                    "lanes": stats.get("lanes"), "batches_rank0": stats.get("batches"), "levels_rank0": stats.get("levels"),
                    "levels_top_down": stats.get("levels_top_down"), "levels_bottom_up": stats.get("levels_bottom_up"),
-                   "parallelism": f"query groups ordered by source degree, contiguous 512-group runs over {world} rank(s), graph replicated",
+                   "parallelism": f"query groups ordered heaviest first, cut into batches, batches over {world} rank(s) ({plan_note}), graph replicated",
                    "l2": "flushed between steps (512 MiB write); CSR larger than L2" if m * 8 > (126 << 20) else "flushed between steps (512 MiB write)"},
         "queries_per_sec": K / (ms_per_step / 1e3),
         "traversed_edges_per_step": traversed_edges_total,
@@ -548,11 +662,15 @@ def run_ours(args, wl, rank, local_rank, world):
                           "csr_build_device_ms": round(eng.stats()["build_ms"], 1)},
         "e2e": {"value": traversed_edges_total / e2e_s / 1e9, "unit": "GTEPS", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": d2h_bytes, "queries_per_sec": K / e2e_s, "ms_per_step": e2e_s * 1e3},
+        "per_rank_device_ms": [round(x, 3) for x in per_rank_ms],
+        "batch_ms_rank0": batch_ms_rank0,
+        "plan": plan_note,
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,
         "kernels": kernels,
         "cpu_baseline": cpu,
+        "reference_gpu": ref_gpu,
         "parity_sample": parity,
     }
     emit(line)
@@ -573,9 +691,12 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work per oracle timing (bounded sample)")
     ap.add_argument("--ref-groups", type=int, default=32, help="groups fed to the reference host build per step")
     ap.add_argument("--ref-seconds", type=float, default=200.0, help="reference arm: CPU seconds for all its steps together")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and reference_gpu legs")
+    ap.add_argument("--ref-gpu-force", action="store_true", help="run the reference's GPU build even where its loader takes minutes")
+    ap.add_argument("--ref-gpu-timeout", type=float, default=1500.0)
     ap.add_argument("--force-port", action="store_true", help="reference arm: always use the oracle port")
     ap.add_argument("--level-log", default="", help="write the per-level counters of the last step (JSON lines)")
+    ap.add_argument("--no-replan", action="store_true", help="keep the snake-order shares (no planning from the warm-up's batch times)")
     ap.add_argument("--contiguous", action="store_true", help="shares in the file's group order instead of the source-degree order")
     ap.add_argument("--opt", action="append", default=[], help="engine option key=value (experiments)")
     ap.add_argument("--alpha", type=int, default=0)
