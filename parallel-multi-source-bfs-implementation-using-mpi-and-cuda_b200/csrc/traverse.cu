@@ -222,6 +222,41 @@ __device__ __forceinline__ void td_push(const TravArgs& a, const LW<NW>& f, long
     }
 }
 
+/* Variant of td_push for G co-operating threads with 128-bit col loads: thread `sub` takes
+ * entries [4 sub, 4 sub + 4) of every 4 G-entry stretch of the row (experiment MSBFS_TD_INT4,
+ * profiles/r2/sweep_f_*: no gain — top-down is bound by the random visited reads and the
+ * atomics, not by the col stream, which the scalar form already reads coalesced). */
+template <int NW, int G>
+__device__ __forceinline__ void td_push_vec(const TravArgs& a, const LW<NW>& f, long long beg, long long end, int sub,
+                                            ull& scanned, ull& fetched, ull& written) {
+    for (long long e4 = (beg & ~3ll) + 4ll * sub; e4 < end; e4 += 4ll * G) {
+        const int4 c = __ldg(reinterpret_cast<const int4*>(a.col + e4));
+        const int u[4] = {c.x, c.y, c.z, c.w};
+        bool ok[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            ok[k] = (e4 + k >= beg) && (e4 + k < end);
+            scanned += ok[k];
+            ok[k] = ok[k] && !test_bit(a.vis_full, u[k]);
+        }
+        LW<NW> vis[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) vis[k] = ok[k] ? lw_load<NW>(a.visited, u[k]) : lw_zero<NW>();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (!ok[k]) continue;
+            ++fetched;
+            const LW<NW> d = lw_andn(f, vis[k]);
+            if (!lw_any(d)) continue;
+#pragma unroll
+            for (int i = 0; i < NW; ++i)
+                if (d.w[i]) atomicOr(&a.acc[(long long)u[k] * NW + i], d.w[i]);
+            ++written;
+            if (!test_bit(a.nxt_nz, u[k])) atomicOr(&a.nxt_nz[u[k] >> 5], 1u << (u[k] & 31));
+        }
+    }
+}
+
 __device__ __forceinline__ void flush_counters(LevelCtrl* c, int slot, ull scanned, ull fetched, ull examined, ull written) { /* per-thread counts may be 32-bit: a thread never scans 2^32 entries in one launch */
     scanned = warp_sum(scanned);
     fetched = warp_sum(fetched);
@@ -252,6 +287,10 @@ __global__ void __launch_bounds__(CTA) td_expand_kernel(TravArgs a, int blk_lo, 
             const LW<NW> f = lw_load<NW>(a.cur, v);
             const long long beg = a.row_ptr[v], end = a.row_ptr[v + 1];
             if (sub == 0) ++examined;
+#ifdef MSBFS_TD_INT4
+            if (G >= 8) td_push_vec<NW, G>(a, f, beg, end, sub, scanned, fetched, written);
+            else
+#endif
             td_push<NW, U>(a, f, beg + sub, end, G, scanned, fetched, written);
         }
     }
@@ -281,7 +320,11 @@ __global__ void __launch_bounds__(CTA) td_heavy_kernel(TravArgs a) {
         const long long beg = a.row_ptr[v] + (long long)k * MSBFS_CHUNK;
         const long long end = min(beg + (long long)MSBFS_CHUNK, a.row_ptr[v + 1]);
         if (lane == 0 && k == 0) ++examined;
+#ifdef MSBFS_TD_INT4
+        td_push_vec<NW, 32>(a, f, beg, end, lane, scanned, fetched, written);
+#else
         td_push<NW, U>(a, f, beg + lane, end, 32, scanned, fetched, written);
+#endif
     }
     flush_counters(a.ctrl, SLOT_TD_HEAVY, scanned, fetched, examined, written);
 }
@@ -402,7 +445,16 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
             continue;
         }
         const int u = (b << 5) + lane;
-        const long long beg = a.row_ptr[u], end = a.row_ptr[u + 1];
+        /* the 33 row offsets of the block staged in shared memory: one coalesced read instead of two
+         * overlapping reads per thread (measured neutral to slightly better, the second read hit L1:
+         * profiles/r2/sweep_f_*; kept as the tidier access pattern) */
+        __shared__ long long s_row[CTA / 32][33];
+        long long* tile = s_row[threadIdx.x >> 5];
+        __syncwarp();
+        tile[lane] = a.row_ptr[u];
+        if (lane == 0) tile[32] = a.row_ptr[u + 32];
+        __syncwarp();
+        const long long beg = tile[lane], end = tile[lane + 1];
         bool has_new = false, full_now = false;
         if (!((fullw >> lane) & 1u) && end > beg) {
             const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
