@@ -283,6 +283,7 @@ extern "C" int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int
 
 extern "C" int msbfs_load_graph_file(msbfs_t* h, const char* path, int32_t* n_out, int64_t* m_out) {
     if (!h || !path) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_load_graph_file: null argument");
+    MsbfsNvtxRange nvtx("msbfs_load_graph_file");
     int rc = set_device(h);
     if (rc) return rc;
     const int fd = open(path, O_RDONLY);
@@ -334,6 +335,7 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
                                     const int32_t* sources) {
     if (!h || num_groups < 0 || (num_groups > 0 && !group_offsets))
         return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_upload_queries: bad argument");
+    MsbfsNvtxRange nvtx("msbfs_upload_queries");
     int rc = set_device(h);
     if (rc) return rc;
     const int64_t base = num_groups > 0 ? group_offsets[0] : 0;
@@ -408,6 +410,7 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
 
 extern "C" int msbfs_run_resident(msbfs_t* h) {
     if (!h) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_run_resident: null handle");
+    MsbfsNvtxRange nvtx("msbfs_run_resident");
     int rc = set_device(h);
     if (rc) return rc;
     return msbfs_traverse(h);

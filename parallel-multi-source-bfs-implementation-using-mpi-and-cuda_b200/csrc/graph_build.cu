@@ -147,6 +147,7 @@ void msbfs_release_graph(msbfs_handle* h) {
 int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const int32_t* d_uv) {
     if (n < 0 || m < 0) return msbfs_fail(MSBFS_ERR_INVALID, "negative graph size");
     if (m > MSBFS_MAX_RECORDS) return msbfs_fail(MSBFS_ERR_RANGE, "graph too large (%lld records)", (long long)m);
+    MsbfsNvtxRange nvtx("msbfs_build_csr");
     cudaStream_t s = h->stream;
     const int T = 256;
 

@@ -1144,6 +1144,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
         const int lanes = std::min(lanes_per_batch, K - group_base);
         L.cur_batch = batches; L.cur_level = -1;
+        MsbfsNvtxRange nvtx_batch("msbfs_batch");
         L.mark_batch();
         L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz, (long long)h->n_active); });
         MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
