@@ -112,6 +112,8 @@ SIGNATURES = {
     "msbfs_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "msbfs_nccl_comm_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "msbfs_nccl_comm_destroy": (C.c_int, [C.c_void_p]),
+    "msbfs_load_graph_file_sharded": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32),
+                                                C.POINTER(C.c_int64)]),
     "msbfs_plan_lanes": (C.c_int, [C.c_int32, C.c_int32]),
     "msbfs_plan_shares": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                     C.POINTER(C.c_int32)]),

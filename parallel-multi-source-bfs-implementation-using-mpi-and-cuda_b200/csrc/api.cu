@@ -240,6 +240,11 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "expect_groups")) {
         if (value < 0) return msbfs_fail(MSBFS_ERR_INVALID, "expect_groups must be >= 0");
         h->opt_expect_groups = (int)std::min<int64_t>(value, 1 << 30);
+    } else if (!std::strcmp(key, "order_key")) {
+        if (value != 0 && value != 1) return msbfs_fail(MSBFS_ERR_INVALID, "order_key must be 0 or 1");
+        h->opt_order_key = (int)value;
+    } else if (!std::strcmp(key, "count_missing")) {
+        h->opt_count_missing = value != 0;
     } else if (!std::strcmp(key, "col_width")) {
         if (value != 0 && value != 4 && value != 8) return msbfs_fail(MSBFS_ERR_INVALID, "col_width must be 0, 4 or 8");
         h->opt_col_width = (int)value;
@@ -281,45 +286,65 @@ extern "C" int msbfs_set_graph_edges(msbfs_t* h, int32_t n, int64_t m, const int
     return rc;
 }
 
+/* Opens a graph file and validates its header (main.cu:94-104): fd, n and m on success. */
+int msbfs_open_graph_file(const char* path, int* fd_out, int32_t* n_out, int64_t* m_out) {
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return msbfs_fail(MSBFS_ERR_IO, "Could not open graph file %s", path); /* main.cu:95-99 */
+    unsigned char hdr[12];
+    if (read(fd, hdr, 12) != 12) { close(fd); return msbfs_fail(MSBFS_ERR_IO, "graph file %s is shorter than its 12-byte header", path); }
+    int32_t n; int64_t m;
+    std::memcpy(&n, hdr, 4);       /* main.cu:102 */
+    std::memcpy(&m, hdr + 4, 8);   /* main.cu:104 */
+    if (n < 0 || m < 0) { close(fd); return msbfs_fail(MSBFS_ERR_FORMAT, "graph file %s has a negative size field", path); }
+    /* before m enters any product: 12 + 8 m and 2 m wrap for a crafted header */
+    if (m > MSBFS_MAX_RECORDS) {
+        close(fd);
+        return msbfs_fail(MSBFS_ERR_RANGE, "graph file %s declares %lld records; the limit is %lld", path, (long long)m,
+                          (long long)MSBFS_MAX_RECORDS);
+    }
+    struct stat stt;
+    if (fstat(fd, &stt) == 0 && S_ISREG(stt.st_mode) && (int64_t)stt.st_size < 12 + 8 * m) {
+        close(fd);
+        return msbfs_fail(MSBFS_ERR_IO, "graph file %s is truncated: %lld records declared, %lld bytes present", path,
+                          (long long)m, (long long)stt.st_size);
+    }
+#ifdef POSIX_FADV_SEQUENTIAL
+    posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
+    *fd_out = fd; *n_out = n; *m_out = m;
+    return MSBFS_OK;
+}
+
+/* Records [first, first + count) of an open graph file -> d_dst, through the pinned staging pipeline. */
+int msbfs_stage_records(msbfs_handle* h, int fd, int64_t first, int64_t count, char* d_dst, const char* what) {
+    const off_t base = (off_t)(12 + 8 * first); /* records start after the 12-byte header */
+    return staged_upload(h, d_dst, 8 * (size_t)count,
+                         [&](char* p, size_t off, size_t len) {
+                             size_t got = 0;
+                             while (got < len) {
+                                 const ssize_t r = pread(fd, p + got, len - got, base + (off_t)(off + got));
+                                 if (r < 0 && errno == EINTR) continue;
+                                 if (r <= 0) return 1;
+                                 got += (size_t)r;
+                             }
+                             return 0;
+                         }, what);
+}
+
 extern "C" int msbfs_load_graph_file(msbfs_t* h, const char* path, int32_t* n_out, int64_t* m_out) {
     if (!h || !path) return msbfs_fail(MSBFS_ERR_INVALID, "msbfs_load_graph_file: null argument");
     MsbfsNvtxRange nvtx("msbfs_load_graph_file");
     int rc = set_device(h);
     if (rc) return rc;
-    const int fd = open(path, O_RDONLY);
-    if (fd < 0) return msbfs_fail(MSBFS_ERR_IO, "Could not open graph file %s", path); /* main.cu:95-99 */
-    struct Closer { int fd; ~Closer() { close(fd); } } closer{fd};
-    unsigned char hdr[12];
-    if (read(fd, hdr, 12) != 12) return msbfs_fail(MSBFS_ERR_IO, "graph file %s is shorter than its 12-byte header", path);
+    int fd = -1;
     int32_t n; int64_t m;
-    std::memcpy(&n, hdr, 4);       /* main.cu:102 */
-    std::memcpy(&m, hdr + 4, 8);   /* main.cu:104 */
-    if (n < 0 || m < 0) return msbfs_fail(MSBFS_ERR_FORMAT, "graph file %s has a negative size field", path);
-    /* before m enters any product: 12 + 8 m and 2 m wrap for a crafted header */
-    if (m > MSBFS_MAX_RECORDS)
-        return msbfs_fail(MSBFS_ERR_RANGE, "graph file %s declares %lld records; the limit is %lld", path, (long long)m,
-                          (long long)MSBFS_MAX_RECORDS);
-    struct stat stt;
-    if (fstat(fd, &stt) == 0 && S_ISREG(stt.st_mode) && (int64_t)stt.st_size < 12 + 8 * m)
-        return msbfs_fail(MSBFS_ERR_IO, "graph file %s is truncated: %lld records declared, %lld bytes present", path,
-                          (long long)m, (long long)stt.st_size);
-#ifdef POSIX_FADV_SEQUENTIAL
-    posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
-#endif
+    rc = msbfs_open_graph_file(path, &fd, &n, &m);
+    if (rc) return rc;
+    struct Closer { int fd; ~Closer() { close(fd); } } closer{fd};
     int32_t* d_uv = nullptr;
     const size_t total = 8 * (size_t)m;
     MSBFS_CUDA(cudaMalloc(&d_uv, std::max<size_t>(total, 8)));
-    rc = staged_upload(h, reinterpret_cast<char*>(d_uv), total,
-                       [&](char* p, size_t off, size_t len) {
-                           size_t got = 0;
-                           while (got < len) { /* records start after the 12-byte header */
-                               const ssize_t r = pread(fd, p + got, len - got, (off_t)(12 + off + got));
-                               if (r < 0 && errno == EINTR) continue;
-                               if (r <= 0) return 1;
-                               got += (size_t)r;
-                           }
-                           return 0;
-                       }, path);
+    rc = msbfs_stage_records(h, fd, 0, m, reinterpret_cast<char*>(d_uv), path);
     if (rc == MSBFS_OK) rc = msbfs_build_from_device_edges(h, n, m, d_uv);
     cudaFree(d_uv);
     if (rc == MSBFS_OK) {
@@ -381,6 +406,13 @@ extern "C" int msbfs_upload_queries(msbfs_t* h, int32_t num_groups, const int64_
         std::vector<long long> cost((size_t)num_groups, 0);
         for (int32_t g = 0; g < num_groups; ++g)
             for (long long i = p_off[g]; i < p_off[g + 1]; ++i) cost[(size_t)g] += p_deg[i];
+        if (h->opt_order_key == 1) { /* spatial proxy: groups ordered by their smallest source id */
+            for (int32_t g = 0; g < num_groups; ++g) {
+                long long lo = INT64_MAX;
+                for (long long i = p_off[g]; i < p_off[g + 1]; ++i) lo = std::min<long long>(lo, p_src[i]);
+                cost[(size_t)g] = -lo;
+            }
+        }
         std::vector<int32_t> order((size_t)num_groups);
         for (int32_t g = 0; g < num_groups; ++g) order[(size_t)g] = g;
         std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) { return cost[(size_t)x] > cost[(size_t)y]; });
@@ -504,6 +536,13 @@ extern "C" int msbfs_group_weights(msbfs_t* h, int32_t num_groups, const int64_t
     if (e != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "msbfs_group_weights: %s", cudaGetErrorString(e));
     for (int32_t g = 0; g < num_groups; ++g)
         for (int64_t i = group_offsets[g] - base; i < group_offsets[g + 1] - base; ++i) out_weights[g] += w[(size_t)i];
+    if (h->opt_order_key == 1) {
+        for (int32_t g = 0; g < num_groups; ++g) {
+            int64_t lo = INT64_MAX;
+            for (int64_t i = group_offsets[g]; i < group_offsets[g + 1]; ++i) lo = std::min<int64_t>(lo, sources[i]);
+            out_weights[g] = -lo;
+        }
+    }
     return MSBFS_OK;
 }
 

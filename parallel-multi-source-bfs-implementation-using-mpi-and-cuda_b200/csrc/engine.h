@@ -66,6 +66,7 @@ struct LevelLog {
 struct LevelCtrl {
     unsigned long long cnt[MSBFS_MAX_LANES];   /* newly visited vertices per lane, this level */
     unsigned long long sums[MSBFS_MAX_LANES];  /* running distance sums per lane              */
+    unsigned long long unvisited[MSBFS_MAX_LANES]; /* active vertices lane j has not reached yet     */
     unsigned long long live[MSBFS_MAX_NW];     /* lanes whose frontier is non-empty           */
     unsigned long long active[MSBFS_MAX_NW];   /* lanes that carry a query group              */
     unsigned long long n_f, m_f;               /* new frontier: vertices, CSR entries         */
@@ -76,6 +77,7 @@ struct LevelCtrl {
     int log_pos;
     unsigned heavy_frontier;                   /* new frontier touches a chunked (hub) row    */
     int last_done, last_next;                  /* device-side copy of the verdict (streak kernel) */
+    int cnt_mode;                              /* what cnt[] holds: 0 = newly visited per lane, 2 = still unvisited per lane */
     /* per-kernel accumulators over a whole run (roofline accounting), see KernelSlot */
     unsigned long long k_scanned[MSBFS_NUM_SLOTS], k_fetched[MSBFS_NUM_SLOTS], k_examined[MSBFS_NUM_SLOTS],
         k_written[MSBFS_NUM_SLOTS];
@@ -107,6 +109,7 @@ struct TravArgs {
     int n_chunk_levels;
     long long n_chunks;
     int n_pad;      /* vertices incl. padding to a multiple of 32 */
+    int n_active;   /* vertices with at least one CSR entry (internal ids [0, n_active)) */
     int blk_heavy;  /* 32-vertex blocks [0, blk_heavy)        : chunked rows    */
     int blk_warp;   /*                 [blk_heavy, blk_warp)  : warp per vertex */
     int blk_g8;     /*                 [blk_warp, blk_g8)     : 8 threads/vertex */
@@ -182,6 +185,8 @@ struct msbfs_handle {
     int opt_reorder = 1;                       /* run groups heaviest-first (by their sources' degrees) */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
+    int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */
+    int opt_count_missing = 1;                 /* after dense bottom-up levels count what lanes still miss instead of the new frontier */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */
     long long opt_alpha = 40;
@@ -199,6 +204,10 @@ struct msbfs_handle {
 /* graph_build.cu */
 int msbfs_build_from_device_edges(msbfs_handle* h, int32_t n, int64_t m, const int32_t* d_uv);
 void msbfs_release_graph(msbfs_handle* h);
+
+/* api.cu: pieces of the loader that comm.cu's sharded load reuses */
+int msbfs_open_graph_file(const char* path, int* fd_out, int32_t* n_out, int64_t* m_out);
+int msbfs_stage_records(msbfs_handle* h, int fd, int64_t first, int64_t count, char* d_dst, const char* what);
 
 /* traverse.cu */
 int msbfs_traverse(msbfs_handle* h);

@@ -149,6 +149,16 @@ __device__ __forceinline__ void flush_full(LevelCtrl* c, ull acc, int lane) {
     if (lane == 0) commit_full(c, acc);
 }
 
+/* The bottom-up kernels know their new frontier as they write it: vertices, their CSR entries and
+ * whether a chunked (hub) row is among them go to the control block here, so that the count pass
+ * that follows is free to count something else (see count_kernel). */
+__device__ __forceinline__ void flush_frontier_totals(LevelCtrl* c, ull nf, ull mf, unsigned heavy, int lane) {
+    nf = warp_sum(nf);
+    mf = warp_sum(mf);
+    if (lane == 0 && nf) { atomicAdd(&c->n_f, nf); atomicAdd(&c->m_f, mf); }
+    if (__any_sync(0xffffffffu, heavy != 0u) && lane == 0) c->heavy_frontier = 1u;
+}
+
 __device__ __forceinline__ bool test_bit(const unsigned* bitmap, int v) {
     return (bitmap[v >> 5] >> (v & 31)) & 1u;
 }
@@ -329,31 +339,90 @@ __global__ void __launch_bounds__(CTA) td_heavy_kernel(TravArgs a) {
     flush_counters(a.ctrl, SLOT_TD_HEAVY, scanned, fetched, examined, written);
 }
 
+/* A warp takes a tile of 32 bitmap words (1024 vertices, one coalesced 128-byte read) and
+ * hands the set bits out densely: round r gives lane j the (32 r + j)-th set bit of the
+ * tile.  With a few frontier vertices per 32-vertex block this keeps all 32 lanes busy
+ * and 32 independent load chains in flight instead of two or three. */
+struct TileBits {
+    unsigned w;      /* this lane's bitmap word */
+    int excl, total; /* set bits in the lanes below / in the whole tile */
+    __device__ __forceinline__ void load(unsigned word, int lane) {
+        w = word;
+        const int cnt = __popc(w);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        excl = incl - cnt;
+        total = __shfl_sync(0xffffffffu, incl, 31);
+    }
+    /* vertex offset inside the tile (0..1023) of set bit number `rank`; all lanes must call */
+    __device__ __forceinline__ int select(int rank) const {
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int cand = lo + step;
+            const int e = __shfl_sync(0xffffffffu, excl, cand & 31);
+            if (cand < 32 && e <= rank) lo = cand;
+        }
+        const unsigned wi = __shfl_sync(0xffffffffu, w, lo);
+        const int ei = __shfl_sync(0xffffffffu, excl, lo);
+        const int r = rank - ei;
+        const int bit = (r >= 0 && r < __popc(wi)) ? (int)__fns(wi, 0, r + 1) : 0;
+        return (lo << 5) + bit;
+    }
+};
+
 /* acc -> new frontier.  acc already excludes visited lanes (td_push masks with
- * ~visited, and visited does not change while a level is expanded). */
+ * ~visited, and visited does not change while a level is expanded).  A warp takes a tile of 1024
+ * vertices of the touched bitmap: where few are touched (the usual top-down level) the set bits
+ * are dealt out densely to the 32 lanes, so every lane has a vertex and 32 independent load
+ * chains are in flight; a densely touched tile is walked block by block, lane = vertex. */
+template <int NW>
+__device__ __forceinline__ void td_finalize_vertex(const TravArgs& a, int v, const LW<NW>& active, ull& full_acc) {
+    const LW<NW> x = lw_load<NW>(a.acc, v);
+    lw_store<NW>(a.acc, v, lw_zero<NW>());
+    const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
+    lw_store<NW>(a.visited, v, nv);
+    lw_store<NW>(a.nxt, v, x);
+    if (lw_covers(nv, active)) {
+        note_full(full_acc, a.row_ptr[v + 1] - a.row_ptr[v]);
+        atomicOr(&a.vis_full[v >> 5], 1u << (v & 31));
+    }
+}
+
 template <int NW>
 __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) {
     const int lane = threadIdx.x & 31;
     const LW<NW> active = lw_from<NW>(a.ctrl->active);
+    const int ntiles = (nblk + 31) >> 5;
     ull full_acc = 0;
-    for (int b = global_warp(); b < nblk; b += total_warps()) {
-        const unsigned w = a.nxt_nz[b];
-        if (w == 0u) continue;
-        bool full_now = false;
-        if ((w >> lane) & 1u) {
-            const int v = (b << 5) + lane;
-            const LW<NW> x = lw_load<NW>(a.acc, v);
-            lw_store<NW>(a.acc, v, lw_zero<NW>());
-            const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
-            lw_store<NW>(a.visited, v, nv);
-            lw_store<NW>(a.nxt, v, x);
-            if (lw_covers(nv, active)) {
-                full_now = true;
-                note_full(full_acc, a.row_ptr[v + 1] - a.row_ptr[v]);
+    if (ntiles < total_warps()) { /* small graph: a 32-vertex block per warp keeps more warps busy than tiles would */
+        for (int b = global_warp(); b < nblk; b += total_warps()) {
+            const unsigned w = a.nxt_nz[b];
+            if ((w >> lane) & 1u) td_finalize_vertex<NW>(a, (b << 5) + lane, active, full_acc);
+        }
+        flush_full(a.ctrl, full_acc, lane);
+        return;
+    }
+    for (int t = global_warp(); t < ntiles; t += total_warps()) {
+        const int b = (t << 5) + lane;
+        TileBits tb;
+        tb.load(b < nblk ? a.nxt_nz[b] : 0u, lane);
+        if (tb.total == 0) continue;
+        if (tb.total > 256) {
+            for (int k = 0; k < 32; ++k) {
+                const unsigned w = __shfl_sync(0xffffffffu, tb.w, k);
+                if ((w >> lane) & 1u) td_finalize_vertex<NW>(a, (t << 10) + (k << 5) + lane, active, full_acc);
+            }
+        } else {
+            for (int r0 = 0; r0 < tb.total; r0 += 32) {
+                const int off = tb.select(r0 + lane); /* warp-collective */
+                if (r0 + lane < tb.total) td_finalize_vertex<NW>(a, (t << 10) + off, active, full_acc);
             }
         }
-        const unsigned fb = __ballot_sync(0xffffffffu, full_now);
-        if (fb && lane == 0) a.vis_full[b] |= fb;
     }
     flush_full(a.ctrl, full_acc, lane);
 }
@@ -437,7 +506,8 @@ template <int NW, int W>
 __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_thread_kernel(TravArgs a, int blk_lo, int blk_hi) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
-    ull full_acc = 0;
+    ull full_acc = 0, nf = 0, mf = 0;
+    unsigned heavy = 0u;
     for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
         const unsigned fullw = a.vis_full[b];
         if (fullw == 0xffffffffu) {
@@ -468,6 +538,8 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
                     lw_store<NW>(a.nxt, u, found);
                     ++written;
                     has_new = true;
+                    ++nf; mf += (ull)(end - beg);
+                    if (b < a.blk_heavy) heavy = 1u;
                     if (lw_covers(nv, lw_from<NW>(a.ctrl->active))) { full_now = true; note_full(full_acc, end - beg); }
                 }
             }
@@ -478,6 +550,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
     }
     flush_counters(a.ctrl, SLOT_BU_G2, scanned, fetched, examined, written);
     flush_full(a.ctrl, full_acc, lane);
+    flush_frontier_totals(a.ctrl, nf, mf, heavy, lane);
 }
 
 /* Rows longer than a.seg entries: one thread per segment of a.seg entries, work items
@@ -530,7 +603,8 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
     const int lane = threadIdx.x & 31;
     const LW<NW> live = lw_from<NW>(a.ctrl->live);
     const LW<NW> active = lw_from<NW>(a.ctrl->active);
-    ull full_acc = 0;
+    ull full_acc = 0, nf = 0, mf = 0;
+    unsigned heavy = 0u;
     for (int b = global_warp(); b < nblk_hub; b += total_warps()) {
         const int u = (b << 5) + lane;
         const unsigned fullw = a.vis_full[b];
@@ -546,7 +620,10 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
                     lw_store<NW>(a.visited, u, nv);
                     lw_store<NW>(a.nxt, u, found);
                     has_new = true;
-                    if (lw_covers(nv, active)) { full_now = true; note_full(full_acc, a.row_ptr[u + 1] - a.row_ptr[u]); }
+                    const long long deg = a.row_ptr[u + 1] - a.row_ptr[u];
+                    ++nf; mf += (ull)deg;
+                    if (b < a.blk_heavy) heavy = 1u;
+                    if (lw_covers(nv, active)) { full_now = true; note_full(full_acc, deg); }
                 }
             }
         }
@@ -558,6 +635,7 @@ __global__ void __launch_bounds__(CTA) bu_heavy_finalize_kernel(TravArgs a, int 
         }
     }
     flush_full(a.ctrl, full_acc, lane);
+    flush_frontier_totals(a.ctrl, nf, mf, heavy, lane);
 }
 
 /* ------------------------------------------- per-lane counts (popcount) --- */
@@ -669,8 +747,17 @@ template <int NW> struct CountShape {
 };
 template <int PW> struct alignas(8 * PW) PartWord { ull w[PW]; };
 
+/* MODE 0 has two ways to get the per-lane counts of a level, chosen on the device:
+ *   - count the NEW frontier words (nxt where nxt_nz): cost ~ frontier vertices;
+ *   - after a bottom-up level (`after_bu`), when fewer vertices remain not-full than entered the
+ *     frontier, count instead the lanes each not-yet-full vertex still MISSES (~visited & active):
+ *     newly visited (j) = unvisited before (j) - unvisited after (j), and the epilogue keeps the
+ *     running `unvisited` per lane.  On the dense levels of a power-law graph (32 M new frontier
+ *     words, 3 M vertices left) that is a tenth of the words.
+ * After a bottom-up level the frontier's vertex / entry totals come from the kernels that wrote
+ * it, so neither way needs them from here. */
 template <int NW, int MODE>
-__global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int degbit, ull* __restrict__ out) {
+__global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int degbit, ull* __restrict__ out, int after_bu, int allow_missing) {
     constexpr int PARTS = CountShape<NW>::PARTS, PW = CountShape<NW>::PW, NC = 2 * PW;
     typedef PartWord<PW> Part;
     __shared__ unsigned s_cnt[64 * NW];
@@ -679,15 +766,16 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
     const int lane = threadIdx.x & 31;
     const int part = global_warp() % PARTS;          /* this warp's slice of every word */
     const int wslot = global_warp() / PARTS, nslots = total_warps() / PARTS;
-    const ull* words = (MODE == 0) ? a.nxt : a.visited;
+    const bool missing = (MODE == 0) && after_bu && allow_missing && a.ctrl->n_u >= 0 && (ull)a.ctrl->n_u < a.ctrl->n_f; /* uniform: both final before this launch */
+    const ull* words = (MODE == 0 && !missing) ? a.nxt : a.visited;
     Csa<NC> csa;
     csa.init();
     int pending = 0;
     ull nf = 0, mf = 0;
     unsigned heavy = 0u;
-    Part zero;
+    Part zero, act;
 #pragma unroll
-    for (int i = 0; i < PW; ++i) zero.w[i] = 0ull;
+    for (int i = 0; i < PW; ++i) { zero.w[i] = 0ull; act.w[i] = missing ? a.ctrl->active[part * PW + i] : 0ull; }
     if (wslot < nslots) {
         for (int b0 = 4 * wslot; b0 < nblk; b0 += 4 * nslots) {
             bool on[4];
@@ -699,7 +787,11 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
                 v[q] = (b << 5) + lane;
                 on[q] = false;
                 if (b < nblk) {
-                    if (MODE == 0) {
+                    if (MODE == 0 && missing) {
+                        const unsigned w = ~a.vis_full[b];
+                        on[q] = ((w >> lane) & 1u) && v[q] < a.n_active;
+                        any |= w;
+                    } else if (MODE == 0) {
                         const unsigned w = a.nxt_nz[b];
                         any |= w;
                         on[q] = (w >> lane) & 1u;
@@ -714,10 +806,15 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
             if (MODE == 0 && any == 0u) continue; /* warp-uniform: the bitmap words are */
             Part x[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
+            for (int q = 0; q < 4; ++q) {
                 x[q] = on[q] ? *reinterpret_cast<const Part*>(words + (long long)v[q] * NW + part * PW) : zero;
+                if (MODE == 0 && missing) {
+#pragma unroll
+                    for (int i = 0; i < PW; ++i) x[q].w[i] = on[q] ? (~x[q].w[i] & act.w[i]) : 0ull;
+                }
+            }
             csa.add4(x[0].w, x[1].w, x[2].w, x[3].w); /* a word that is off is zero and adds nothing */
-            if (MODE == 0 && part == 0) {
+            if (MODE == 0 && !after_bu && part == 0) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     if (on[q]) { ++nf; mf += (ull)(a.row_ptr[v[q] + 1] - a.row_ptr[v[q]]); }
@@ -739,10 +836,13 @@ __global__ void __launch_bounds__(CTA) count_kernel(TravArgs a, int nblk, int de
         }
     }
     if (MODE == 0) {
-        nf = warp_sum(nf);
-        mf = warp_sum(mf);
-        if (lane == 0 && nf) { atomicAdd(&a.ctrl->n_f, nf); atomicAdd(&a.ctrl->m_f, mf); }
-        if (__any_sync(0xffffffffu, heavy != 0u) && lane == 0) a.ctrl->heavy_frontier = 1u;
+        if (missing && blockIdx.x == 0 && threadIdx.x == 0) a.ctrl->cnt_mode = 2;
+        if (!after_bu) {
+            nf = warp_sum(nf);
+            mf = warp_sum(mf);
+            if (lane == 0 && nf) { atomicAdd(&a.ctrl->n_f, nf); atomicAdd(&a.ctrl->m_f, mf); }
+            if (__any_sync(0xffffffffu, heavy != 0u) && lane == 0) a.ctrl->heavy_frontier = 1u;
+        }
     }
 }
 
@@ -752,6 +852,7 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long l
     const int j = threadIdx.x; /* MSBFS_MAX_LANES threads */
     c->cnt[j] = 0ull;
     c->sums[j] = 0ull;
+    c->unvisited[j] = (j < lanes) ? (ull)n_active : 0ull;
     if (j < MSBFS_MAX_NW) {
         c->live[j] = 0ull;
         ull m = 0ull;
@@ -761,7 +862,7 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long l
         c->active[j] = m;
     }
     if (j == 0) {
-        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->n_u = n_active; c->heavy_frontier = 0u;
+        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->n_u = n_active; c->heavy_frontier = 0u; c->cnt_mode = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level = -1;
     }
@@ -773,8 +874,16 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long l
 __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int log_cap, LevelVerdict* verdict,
                                               int direction, long long alpha, int force_direction) {
     /* any block size that is a multiple of 32 */
+    const int cnt_mode = c->cnt_mode; /* read by everyone before thread 0 resets it below */
     for (int j = threadIdx.x; j < MSBFS_MAX_LANES; j += blockDim.x) {
-        const ull cnt = c->cnt[j];
+        ull cnt = c->cnt[j];
+        if (cnt_mode == 2) { /* cnt[] holds what lane j still misses: newly visited = the difference */
+            const ull after = cnt;
+            cnt = c->unvisited[j] - after;
+            c->unvisited[j] = after;
+        } else {
+            c->unvisited[j] -= cnt;
+        }
         c->sums[j] += (ull)(c->level + 1) * cnt;
         c->cnt[j] = 0ull;
         const unsigned bal = __ballot_sync(0xffffffffu, cnt != 0ull);
@@ -807,6 +916,7 @@ __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int l
         c->last_done = (nf == 0ull);
         c->last_next = next;
         c->heavy_frontier = 0u;
+        c->cnt_mode = 0;
         c->n_f = 0; c->m_f = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level += 1;
@@ -829,42 +939,6 @@ __global__ void epilogue_kernel(LevelCtrl* c, LevelLog* log, int log_cap, LevelV
  * every row is short (max degree <= option "streak_max_deg", default 256), so a frontier vertex is one thread.
  * On return the host finds ctrl / verdict exactly as after a normal epilogue, plus the
  * number of levels run (the frontier buffers have swapped that many times). */
-
-/* A warp takes a tile of 32 bitmap words (1024 vertices, one coalesced 128-byte read) and
- * hands the set bits out densely: round r gives lane j the (32 r + j)-th set bit of the
- * tile.  With a few frontier vertices per 32-vertex block this keeps all 32 lanes busy
- * and 32 independent load chains in flight instead of two or three. */
-struct TileBits {
-    unsigned w;      /* this lane's bitmap word */
-    int excl, total; /* set bits in the lanes below / in the whole tile */
-    __device__ __forceinline__ void load(unsigned word, int lane) {
-        w = word;
-        const int cnt = __popc(w);
-        int incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        excl = incl - cnt;
-        total = __shfl_sync(0xffffffffu, incl, 31);
-    }
-    /* vertex offset inside the tile (0..1023) of set bit number `rank`; all lanes must call */
-    __device__ __forceinline__ int select(int rank) const {
-        int lo = 0;
-#pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-            const int cand = lo + step;
-            const int e = __shfl_sync(0xffffffffu, excl, cand & 31);
-            if (cand < 32 && e <= rank) lo = cand;
-        }
-        const unsigned wi = __shfl_sync(0xffffffffu, w, lo);
-        const int ei = __shfl_sync(0xffffffffu, excl, lo);
-        const int r = rank - ei;
-        const int bit = (r >= 0 && r < __popc(wi)) ? (int)__fns(wi, 0, r + 1) : 0;
-        return (lo << 5) + bit;
-    }
-};
 
 template <int NW>
 __global__ void __launch_bounds__(CTA, (NW == 8) ? 2 : 4) td_streak_kernel(TravArgs a, LevelLog* log, int log_cap, LevelVerdict* verdict,
@@ -1109,7 +1183,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk; a.vis_full = h->d_bitmaps + 2 * (size_t)nblk;
     a.ctrl = h->d_ctrl;
     a.chunk_level_base = h->d_chunk_level_base; a.n_chunk_levels = h->n_chunk_levels; a.n_chunks = h->n_chunks;
-    a.n_pad = h->n_pad;
+    a.n_pad = h->n_pad; a.n_active = h->n_active;
     a.blk_heavy = h->blk_heavy; a.blk_warp = h->blk_warp; a.blk_g8 = h->blk_g8; a.blk_end = h->blk_end;
     a.seg_level_base = h->d_seg_level_base; a.n_seg_levels = h->n_seg_levels; a.n_seg_items = h->n_seg_items;
     a.seg = h->seg; a.blk_multi = h->blk_multi;
@@ -1156,7 +1230,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                                                                       h->d_q_sources, group_base, lanes);
         });
         L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
-        L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
+        L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr, 0, 0); });
         L.timed(SLOT_OTHER, [&] {
             epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, 0, h->opt_alpha,
                                                            h->opt_direction);
@@ -1226,7 +1300,9 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                         k_thread<<<L.grid_for_warps(a.blk_end - a.blk_multi), CTA, 0, s>>>(a, a.blk_multi, a.blk_end);
                     });
             }
-            L.timed(SLOT_COUNT, [&] { count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr); });
+            L.timed(SLOT_COUNT, [&] {
+                count_kernel<NW, 0><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, 0, nullptr, dir == 2 ? 1 : 0, h->opt_count_missing);
+            });
             L.timed(SLOT_OTHER, [&] {
                 epilogue_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, h->d_log, h->log_cap, h->h_verdict, dir,
                                                                h->opt_alpha, h->opt_direction);
@@ -1239,7 +1315,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
         if (want_reached) {
             MSBFS_CUDA(cudaMemsetAsync(d_reached, 0, sizeof(ull) * MSBFS_MAX_LANES, s));
             for (int bit = 0; bit < 40; ++bit)
-                count_kernel<NW, 1><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, bit, d_reached);
+                count_kernel<NW, 1><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, bit, d_reached, 0, 0);
             ull tmp[MSBFS_MAX_LANES];
             MSBFS_CUDA(cudaMemcpyAsync(tmp, d_reached, sizeof tmp, cudaMemcpyDeviceToHost, s));
             MSBFS_CUDA(cudaStreamSynchronize(s));

@@ -32,8 +32,11 @@
 #include <cstring>
 #include <iomanip>
 #include <iostream>
+#include <sstream>
 #include <string>
 #include <vector>
+
+#include <unistd.h>
 
 using namespace std;
 
@@ -44,6 +47,12 @@ static void die(int rank, const char* what) {
 
 int main(int argc, char* argv[]) {
     MPI_Init(&argc, &argv);
+    /* The seven report lines are this program's contract on stdout.  Libraries underneath may
+     * write there too (NCCL prints a version banner at its first communicator), so the report
+     * gets a private copy of the original stdout and descriptor 1 is pointed at stderr. */
+    fflush(stdout);
+    const int report_fd = dup(1);
+    if (report_fd >= 0) dup2(2, 1);
     int world_size = 1, world_rank = 0;
     MPI_Comm_size(MPI_COMM_WORLD, &world_size);
     MPI_Comm_rank(MPI_COMM_WORLD, &world_rank);
@@ -102,6 +111,28 @@ int main(int argc, char* argv[]) {
         if (lanes > 0) msbfs_set_option(eng, "lanes", lanes);
         else msbfs_set_option(eng, "expect_groups", K);
     }
+    /* NCCL when every rank has a GPU of its own (np <= gn): rank 0's ncclUniqueId travels by
+     * MPI_Bcast.  The communicator carries the edge all-gather of the sharded load below and the
+     * packed-min reduction at the end.  With ranks sharing a device (np > gn) NCCL cannot form
+     * a communicator and MPI carries the 8 bytes.  Set up inside the preprocessing window,
+     * first collective included (NCCL connects its channels lazily; that belongs here, not in
+     * the computation window).  MSBFS_NO_NCCL=1 forces the MPI path. */
+    void* nccl_comm = nullptr;
+    if (world_size > 1 && world_size <= numGPU && !getenv("MSBFS_NO_NCCL")) {
+        unsigned char id[MSBFS_NCCL_ID_BYTES];
+        int ok = 1;
+        if (world_rank == 0 && msbfs_nccl_unique_id(id) != MSBFS_OK) ok = 0;
+        MPI_Bcast(&ok, 1, MPI_INT, 0, MPI_COMM_WORLD);
+        if (ok) {
+            MPI_Bcast(id, MSBFS_NCCL_ID_BYTES, MPI_BYTE, 0, MPI_COMM_WORLD);
+            if (msbfs_nccl_comm_create(eng, id, world_size, world_rank, &nccl_comm) != MSBFS_OK) die(world_rank, "NCCL communicator");
+            uint64_t warm = 0;
+            if (msbfs_allreduce_min_u64(eng, nccl_comm, &warm) != MSBFS_OK) die(world_rank, "NCCL warm-up");
+        } else if (world_rank == 0) {
+            fprintf(stderr, "NCCL unavailable (%s): reducing over MPI\n", msbfs_last_error());
+        }
+    }
+
     int32_t n = 0;
     int64_t m = 0;
     /* One CSR per GPU (replaces the per-rank upload of main.cu:283-291): the lowest rank on a
@@ -110,7 +141,14 @@ int main(int argc, char* argv[]) {
     const bool share = world_size > numGPU && !getenv("MSBFS_NO_IPC");
     const bool owner = !share || world_rank < numGPU;
     bool graph_shared = false;
-    if (owner && msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
+    /* With a communicator the file is read once per box, not once per rank: every rank reads
+     * 1/np of the records and an all-gather over NVLink completes the edge list on every GPU
+     * (MSBFS_NO_SHARDED_LOAD=1: every rank reads the whole file). */
+    const bool sharded = nccl_comm && !getenv("MSBFS_NO_SHARDED_LOAD");
+    if (sharded) {
+        if (msbfs_load_graph_file_sharded(eng, graphFile.c_str(), nccl_comm, world_rank, world_size, &n, &m) != MSBFS_OK)
+            die(world_rank, "graph file");
+    } else if (owner && msbfs_load_graph_file(eng, graphFile.c_str(), &n, &m) != MSBFS_OK) die(world_rank, "graph file");
     if (share) {
         for (int d = 0; d < numGPU; ++d) { /* rank d owns device d */
             long long size = 0;
@@ -134,27 +172,6 @@ int main(int argc, char* argv[]) {
             }
         }
     }
-
-    /* Result reduction over NCCL / NVLink when every rank has a GPU of its own (np <= gn):
-     * rank 0's ncclUniqueId travels by MPI_Bcast.  With ranks sharing a device (np > gn) NCCL
-     * cannot form a communicator and MPI carries the 8 bytes.  The communicator is set up
-     * inside the preprocessing window (the reference sets up its Pair datatype in the
-     * computation window, main.cu:326-328; this is the dearer of the two places to charge it).
-     * MSBFS_NO_NCCL=1 forces the MPI path. */
-    void* nccl_comm = nullptr;
-    if (world_size > 1 && world_size <= numGPU && !getenv("MSBFS_NO_NCCL")) {
-        unsigned char id[MSBFS_NCCL_ID_BYTES];
-        int ok = 1;
-        if (world_rank == 0 && msbfs_nccl_unique_id(id) != MSBFS_OK) ok = 0;
-        MPI_Bcast(&ok, 1, MPI_INT, 0, MPI_COMM_WORLD);
-        if (ok) {
-            MPI_Bcast(id, MSBFS_NCCL_ID_BYTES, MPI_BYTE, 0, MPI_COMM_WORLD);
-            if (msbfs_nccl_comm_create(eng, id, world_size, world_rank, &nccl_comm) != MSBFS_OK) die(world_rank, "NCCL communicator");
-        } else if (world_rank == 0) {
-            fprintf(stderr, "NCCL unavailable (%s): reducing over MPI\n", msbfs_last_error());
-        }
-    }
-
 
     /* every rank ready before the clock stops, as the reference's broadcasts imply */
     MPI_Barrier(MPI_COMM_WORLD);
@@ -232,15 +249,22 @@ int main(int argc, char* argv[]) {
     double computation_time = chrono::duration<double>(end_computation - start_computation).count();
 
     if (world_rank == 0) { /* main.cu:403-414 */
-        cout << fixed << setprecision(9);
-        cout << "Graph: " << graphFile << "\n";
-        cout << "Query: " << queryFile << "\n";
-        cout << "Query number (k) with minimum F value: " << (minK + 1) << "\n";
-        cout << "Minimum F value: " << minF << "\n";
-        cout << "GPU # : " << numGPU << " GPU\n";
-        cout << "Preprocessing time: " << preprocessing_time << " s\n";
-        cout << "Computation time: " << computation_time << " s\n";
-        cout.flush();
+        ostringstream out;
+        out << fixed << setprecision(9);
+        out << "Graph: " << graphFile << "\n";
+        out << "Query: " << queryFile << "\n";
+        out << "Query number (k) with minimum F value: " << (minK + 1) << "\n";
+        out << "Minimum F value: " << minF << "\n";
+        out << "GPU # : " << numGPU << " GPU\n";
+        out << "Preprocessing time: " << preprocessing_time << " s\n";
+        out << "Computation time: " << computation_time << " s\n";
+        const string text = out.str();
+        size_t done = 0;
+        while (done < text.size()) {
+            const ssize_t w = write(report_fd >= 0 ? report_fd : 1, text.data() + done, text.size() - done);
+            if (w <= 0) break;
+            done += (size_t)w;
+        }
     }
 
     if (!dumpFile.empty()) { /* opt-in: all F values on rank 0 */
@@ -267,13 +291,16 @@ int main(int argc, char* argv[]) {
 
     if (getenv("MSBFS_STATS")) {
         msbfs_stats st;
-        if (msbfs_get_stats(eng, &st) == MSBFS_OK)
-            fprintf(stderr,
+        if (msbfs_get_stats(eng, &st) == MSBFS_OK) {
+            char line[1024]; /* one write per rank, so that the ranks' lines do not interleave */
+            const int len = snprintf(line, sizeof line,
                     "[rank %d] groups=%d lanes=%d batches=%d levels=%lld (td %lld, bu %lld) scanned td=%lld bu=%lld "
-                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f reduce=%s graph=%s\n",
+                    "alg_bytes=%lld launches=%lld build_ms=%.3f run_ms=%.3f reduce=%s graph=%s load=%s\n",
                     world_rank, mine, st.lanes, st.batches, (long long)st.levels, (long long)st.levels_top_down,
                     (long long)st.levels_bottom_up, (long long)st.scanned_top_down, (long long)st.scanned_bottom_up,
-                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms, nccl_comm ? "nccl" : "mpi", graph_shared ? "shared" : "own");
+                    (long long)st.alg_bytes, (long long)st.kernel_launches, st.build_ms, st.run_ms, nccl_comm ? "nccl" : "mpi", graph_shared ? "shared" : "own", sharded ? "sharded" : "whole");
+            if (len > 0 && write(2, line, (size_t)min<int>(len, (int)sizeof line - 1)) < 0) { /* nothing to do about it */ }
+        }
     }
 
     msbfs_nccl_comm_destroy(nccl_comm);

@@ -106,7 +106,9 @@ def test_ranks_on_one_gpu_share_one_csr(pkg, ob, expected, tmp_path):
 @pytest.mark.gpu
 def test_nccl_reduce_in_the_drop_in_two_gpus(pkg, ob, expected, tmp_path):
     """`mpirun -np 2 ... -gn 2`: the packed-min reduction runs over NCCL (communicator made from
-    an ncclUniqueId broadcast over MPI); MSBFS_NO_NCCL=1 keeps MPI.  Needs two GPUs."""
+    an ncclUniqueId broadcast over MPI) and the graph file is read once per box (sharded read +
+    ncclAllGather of the edge records); MSBFS_NO_SHARDED_LOAD=1 / MSBFS_NO_NCCL=1 fall back to a
+    whole-file read per rank / the MPI reduction.  Same seven report lines every way.  Needs two GPUs."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
@@ -116,14 +118,19 @@ def test_nccl_reduce_in_the_drop_in_two_gpus(pkg, ob, expected, tmp_path):
     gpath = str(tmp_path / "g.bin")
     qpath = os.path.join(os.path.dirname(__file__), "golden", expected[name]["query_file"])
     pkg.write_graph_file(gpath, n, uv)
-    for no_nccl in (False, True):
-        env = dict(os.environ, MSBFS_STATS="1")
-        if no_nccl:
+    for mode in ("nccl", "nccl-whole-file", "mpi"):
+        env = dict(os.environ, MSBFS_STATS="1", NCCL_DEBUG="VERSION")  # NCCL's banner must not reach the report
+        if mode == "mpi":
             env["MSBFS_NO_NCCL"] = "1"
+        if mode == "nccl-whole-file":
+            env["MSBFS_NO_SHARDED_LOAD"] = "1"
         res = subprocess.run([mpirun, "-np", "2", main, "-g", gpath, "-q", qpath, "-gn", "2"], capture_output=True, text=True,
                              timeout=300, env=env)
         assert res.returncode == 0, res.stderr
         m = REPORT.match(res.stdout)
         assert m and int(m["k"]) == expected[name]["k_printed"] and int(m["f"]) == expected[name]["min_f"], res.stdout
-        want = "reduce=mpi" if no_nccl else "reduce=nccl"
+        want = "reduce=mpi" if mode == "mpi" else "reduce=nccl"
         assert sum(want in ln for ln in res.stderr.splitlines()) == 2, res.stderr
+        # with a communicator each rank reads half of the file and an all-gather completes the edge list
+        load = "load=sharded" if mode == "nccl" else "load=whole"
+        assert sum(load in ln for ln in res.stderr.splitlines()) == 2, res.stderr
