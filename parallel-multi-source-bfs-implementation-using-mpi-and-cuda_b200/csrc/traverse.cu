@@ -1338,6 +1338,21 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
 /* Buffers are sized for `nw` 64-bit words per lane word and serve any narrower width too
  * (every kernel strides by its own NW; acc / hub_acc are all-zero whatever the width). */
+/* The runtime loads a kernel's code at its first launch; asking for its attributes loads it now.
+ * Called when the traversal state is sized (graph load, the preprocessing window), so that the
+ * first run does not pay a few milliseconds of module loading per kernel in its level loop. */
+template <int NW> void preload_kernels() {
+    cudaFuncAttributes at;
+    const void* fns[] = {(const void*)inject_kernel<NW>, (const void*)td_expand_kernel<NW, 32, 4>, (const void*)td_expand_kernel<NW, 8, 4>,
+                         (const void*)td_expand_kernel<NW, 2, 4>, (const void*)td_heavy_kernel<NW, 4>, (const void*)td_finalize_kernel<NW>,
+                         (const void*)bu_thread_kernel<NW, 4>, (const void*)bu_thread_kernel<NW, 8>, (const void*)bu_segment_kernel<NW, 4>,
+                         (const void*)bu_segment_kernel<NW, 8>, (const void*)bu_heavy_finalize_kernel<NW>, (const void*)count_kernel<NW, 0>,
+                         (const void*)td_streak_kernel<NW>, (const void*)init_batch_kernel, (const void*)epilogue_kernel,
+                         (const void*)store_sums_kernel};
+    for (const void* f : fns) cudaFuncGetAttributes(&at, f);
+    cudaGetLastError();
+}
+
 int ensure_traversal_buffers(msbfs_handle* h, int nw) {
     if (h->nw_alloc >= nw && h->d_visited) return MSBFS_OK;
     msbfs_release_traversal(h);
@@ -1359,6 +1374,7 @@ int ensure_traversal_buffers(msbfs_handle* h, int nw) {
     MSBFS_CUDA(cudaMemsetAsync(h->d_hub_acc, 0, hub_bytes, s));   /* invariant: zero between kernels */
     MSBFS_CUDA(cudaMemsetAsync(h->d_ctrl, 0, sizeof(LevelCtrl), s));
     h->nw_alloc = nw;
+    if (nw == 1) preload_kernels<1>(); else if (nw == 2) preload_kernels<2>(); else if (nw == 8) preload_kernels<8>(); else preload_kernels<4>();
 
     /* Blackwell's 126 MB L2: keep the three bitmaps (n/8 bytes each — every random
      * probe of the traversal hits them first) resident with an access-policy window. */

