@@ -64,8 +64,6 @@ int msbfs_destroy(msbfs_t* h);
  *   "order_key"  what "reorder" sorts the groups by: 0 = two-hop weight of their sources (default),
  *                1 = smallest source id, a locality proxy for graphs whose ids are spatial
  *                (lattices, road networks); measured without effect on the 4096^2 lattice
- *   "dense_prefix"  1 = bottom-up scans take entries below the frontier bitmap's all-ones prefix as
- *                hits without probing the bitmap (default), 0 = always probe
  *   "count_missing"  1 = after a bottom-up level that leaves fewer vertices unfinished than it put
  *                into the frontier, take the per-lane counts from what the unfinished vertices
  *                still miss instead of from the new frontier words (default), 0 = always the latter

@@ -77,7 +77,6 @@ struct LevelCtrl {
     int log_pos;
     unsigned heavy_frontier;                   /* new frontier touches a chunked (hub) row    */
     int last_done, last_next;                  /* device-side copy of the verdict (streak kernel) */
-    int dense_prefix;                          /* vertices [0, dense_prefix) are ALL in the frontier a bottom-up level reads */
     int cnt_mode;                              /* what cnt[] holds: 0 = newly visited per lane, 2 = still unvisited per lane */
     /* per-kernel accumulators over a whole run (roofline accounting), see KernelSlot */
     unsigned long long k_scanned[MSBFS_NUM_SLOTS], k_fetched[MSBFS_NUM_SLOTS], k_examined[MSBFS_NUM_SLOTS],
@@ -111,7 +110,6 @@ struct TravArgs {
     long long n_chunks;
     int n_pad;      /* vertices incl. padding to a multiple of 32 */
     int n_active;   /* vertices with at least one CSR entry (internal ids [0, n_active)) */
-    int use_dense_prefix; /* bottom-up scans may trust ctrl->dense_prefix */
     int blk_heavy;  /* 32-vertex blocks [0, blk_heavy)        : chunked rows    */
     int blk_warp;   /*                 [blk_heavy, blk_warp)  : warp per vertex */
     int blk_g8;     /*                 [blk_warp, blk_g8)     : 8 threads/vertex */
@@ -188,7 +186,6 @@ struct msbfs_handle {
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
     int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */
-    int opt_dense_prefix = 1;                  /* bottom-up scans skip the bitmap probe below the frontier's all-ones prefix */
     int opt_count_missing = 1;                 /* after dense bottom-up levels count what lanes still miss instead of the new frontier */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */

@@ -441,14 +441,11 @@ __global__ void __launch_bounds__(CTA) td_finalize_kernel(TravArgs a, int nblk) 
 template <int W> struct alignas(4 * W) ColVec { int v[W]; };
 
 /* W = col entries per load (4: one 128-bit load, 8: one 256-bit load). */
-/* D = the frontier's dense prefix: every vertex below D is in the frontier (dense_prefix_kernel), so
- * an entry below D is a hit without looking — on power-law graphs the hubs, which is where most
- * entries point, and the probe is one LSU wavefront per entry (DESIGN.md "Where the time goes"). */
 template <int NW, int W>
-__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, int D, long long beg, long long end,
+__device__ __forceinline__ LW<NW> bu_scan_row(const TravArgs& a, long long beg, long long end,
                                               const LW<NW>& need, unsigned& scanned, unsigned& fetched) {
     typedef ColVec<W> CV;
-    auto probe = [&](int v) -> unsigned { return (v < D) ? 0xffffffffu : a.cur_nz[v >> 5]; };
+    auto probe = [&](int v) -> unsigned { return a.cur_nz[v >> 5]; };
     LW<NW> acc = lw_zero<NW>();
     long long e = beg & ~(long long)(W - 1);
     CV c = *reinterpret_cast<const CV*>(a.col + e);
@@ -502,18 +499,6 @@ __device__ __forceinline__ void bu_store_block_bits(const TravArgs& a, int b, in
     }
 }
 
-/* Length of the all-ones prefix of the frontier bitmap, in vertices: the first word that is not
- * 0xffffffff ends it.  The epilogue of the previous level has reset ctrl->dense_prefix to INT_MAX
- * ("no hole seen"); a handful of microseconds before the bottom-up kernels of a level. */
-__global__ void __launch_bounds__(CTA) dense_prefix_kernel(const unsigned* __restrict__ bitmap, int nblk, LevelCtrl* c) {
-    int first = nblk;
-    for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += gridDim.x * blockDim.x) {
-        if (bitmap[b] != 0xffffffffu) { first = b; break; }
-        if (b >= (c->dense_prefix >> 5)) break; /* someone has already found an earlier hole */
-    }
-    if (first < nblk) atomicMin(&c->dense_prefix, first << 5);
-}
-
 /* Rows of at most MSBFS_DEG_G8 entries: one thread per vertex, no cross-thread
  * traffic at all.  The 32 visited words of a block are one contiguous 1 KB read, and
  * each thread leaves its loop as soon as its own need is covered. */
@@ -523,7 +508,6 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
     ull full_acc = 0, nf = 0, mf = 0;
     unsigned heavy = 0u;
-    const int D = a.use_dense_prefix ? a.ctrl->dense_prefix : 0;
     for (int b = blk_lo + global_warp(); b < blk_hi; b += total_warps()) {
         const unsigned fullw = a.vis_full[b];
         if (fullw == 0xffffffffu) {
@@ -546,7 +530,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
             const LW<NW> need = lw_andn(lw_from<NW>(a.ctrl->live), lw_load<NW>(a.visited, u));
             if (lw_any(need)) {
                 ++examined;
-                const LW<NW> acc = bu_scan_row<NW, W>(a, D, beg, end, need, scanned, fetched);
+                const LW<NW> acc = bu_scan_row<NW, W>(a, beg, end, need, scanned, fetched);
                 const LW<NW> found = lw_and(acc, need);
                 if (lw_any(found)) {
                     const LW<NW> nv = lw_or(lw_load<NW>(a.visited, u), found);
@@ -579,7 +563,6 @@ template <int NW, int W>
 __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLOCKS : 4) bu_segment_kernel(TravArgs a) {
     const int lane = threadIdx.x & 31;
     unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
-    const int D = a.use_dense_prefix ? a.ctrl->dense_prefix : 0;
     for (long long c0 = 32ll * global_warp(); c0 < a.n_seg_items; c0 += 32ll * total_warps()) {
         const long long c = c0 + lane;
         if (c >= a.n_seg_items) continue;
@@ -602,7 +585,7 @@ __global__ void __launch_bounds__(CTA, (NW == 1) ? 6 : (NW == 8) ? MSBFS_NW8_BLO
         if (!lw_any(need)) continue;
         const long long beg = a.row_ptr[u] + (long long)k * a.seg;
         const long long end = min(beg + (long long)a.seg, a.row_ptr[u + 1]);
-        const LW<NW> acc = bu_scan_row<NW, W>(a, D, beg, end, need, scanned, fetched);
+        const LW<NW> acc = bu_scan_row<NW, W>(a, beg, end, need, scanned, fetched);
         const LW<NW> found = lw_and(acc, need);
         if (lw_any(found)) {
 #pragma unroll
@@ -879,7 +862,7 @@ __global__ void init_batch_kernel(LevelCtrl* c, int lanes, long long nnz, long l
         c->active[j] = m;
     }
     if (j == 0) {
-        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->n_u = n_active; c->heavy_frontier = 0u; c->cnt_mode = 0; c->dense_prefix = 0x7fffffff;
+        c->n_f = 0; c->m_f = 0; c->m_u = nnz; c->n_u = n_active; c->heavy_frontier = 0u; c->cnt_mode = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level = -1;
     }
@@ -934,7 +917,6 @@ __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int l
         c->last_next = next;
         c->heavy_frontier = 0u;
         c->cnt_mode = 0;
-        c->dense_prefix = 0x7fffffff;
         c->n_f = 0; c->m_f = 0;
         c->scanned = c->words_fetched = c->examined = c->words_written = 0;
         c->level += 1;
@@ -1201,7 +1183,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     a.cur_nz = h->d_bitmaps; a.nxt_nz = h->d_bitmaps + nblk; a.vis_full = h->d_bitmaps + 2 * (size_t)nblk;
     a.ctrl = h->d_ctrl;
     a.chunk_level_base = h->d_chunk_level_base; a.n_chunk_levels = h->n_chunk_levels; a.n_chunks = h->n_chunks;
-    a.n_pad = h->n_pad; a.n_active = h->n_active; a.use_dense_prefix = h->opt_dense_prefix;
+    a.n_pad = h->n_pad; a.n_active = h->n_active;
     a.blk_heavy = h->blk_heavy; a.blk_warp = h->blk_warp; a.blk_g8 = h->blk_g8; a.blk_end = h->blk_end;
     a.seg_level_base = h->d_seg_level_base; a.n_seg_levels = h->n_seg_levels; a.n_seg_items = h->n_seg_items;
     a.seg = h->seg; a.blk_multi = h->blk_multi;
@@ -1304,9 +1286,6 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                 L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
             } else {
                 ++levels_bu;
-                /* the frontier's dense prefix for this level's scans (the epilogue has reset it) */
-                if (a.use_dense_prefix)
-                    L.timed(SLOT_OTHER, [&] { dense_prefix_kernel<<<std::min(64, (nblk + CTA - 1) / CTA), CTA, 0, s>>>(a.cur_nz, nblk, h->d_ctrl); });
                 if (a.blk_multi > 0) {
                     if (a.n_seg_items > 0)
                         L.timed(SLOT_BU_HEAVY, [&] {
