@@ -64,6 +64,11 @@ int msbfs_destroy(msbfs_t* h);
  *   "order_key"  what "reorder" sorts the groups by: 0 = two-hop weight of their sources (default),
  *                1 = smallest source id, a locality proxy for graphs whose ids are spatial
  *                (lattices, road networks); measured without effect on the 4096^2 lattice
+ *   "lane_major"  the sparse per-group engine for road-like graphs (a visited bitmap per group and a
+ *                queue of (group, vertex) pairs, one persistent kernel per batch): -1 = when every
+ *                row has at most 16 entries (default), 0 = never, 1 = on any graph whose longest
+ *                row fits "streak_max_deg"; a batch whose level outgrows the queue (2 x the
+ *                non-isolated vertices) is redone by the bit-parallel engine
  *   "count_missing"  1 = after a bottom-up level that leaves fewer vertices unfinished than it put
  *                into the frontier, take the per-lane counts from what the unfinished vertices
  *                still miss instead of from the new frontier words (default), 0 = always the latter
@@ -277,7 +282,8 @@ typedef struct msbfs_kernel_profile {
 
 /* One record per BFS level of the last run (all batches, in execution order); the
  * counters behind MSBFS_STATS and the roofline accounting.  direction: 0 = source
- * injection, 1 = top-down, 2 = bottom-up.  Returns the number of records through
+ * injection, 1 = top-down, 2 = bottom-up, 3 = a level of the lane-major engine (scanned = CSR entries read,
+ * vertices_examined = (group, vertex) visits, words_written = newly visited).  Returns the number of records through
  * count_out (at most `capacity` are copied). */
 typedef struct msbfs_level_record {
     int32_t  level;

@@ -45,7 +45,7 @@ constexpr int MSBFS_DEG_G8      = 8;     /* deg >  this: 8 threads per vertex, e
 /* kernels that are timed / accounted separately */
 enum KernelSlot {
     SLOT_TD_HEAVY = 0, SLOT_TD_G32, SLOT_TD_G8, SLOT_TD_G2,
-    SLOT_BU_HEAVY, SLOT_BU_G32, SLOT_BU_G8, SLOT_BU_G2,
+    SLOT_BU_HEAVY, SLOT_LANE_MAJOR, SLOT_BU_G8, SLOT_BU_G2,
     SLOT_TD_FINALIZE, SLOT_BU_HEAVY_FINALIZE, SLOT_COUNT, SLOT_OTHER,
     MSBFS_NUM_SLOTS
 };
@@ -156,6 +156,15 @@ struct msbfs_handle {
     int log_cap = 0;
     LevelVerdict* h_verdict = nullptr; /* pinned */
 
+    /* lane-major engine for road-like graphs (lane_major.cu): a visited bitmap per group, two
+     * queues of (group, vertex) pairs, a control block */
+    unsigned int* d_lm_bits = nullptr;
+    unsigned long long* d_lm_q[2] = {nullptr, nullptr};
+    void* d_lm_ctrl = nullptr;
+    int lm_lanes = 0, lm_grid = 0;
+    long long lm_cap = 0;
+    int64_t lm_expanded = 0, lm_scanned = 0, lm_fresh = 0; /* totals of the last run's lane-major batches */
+
     /* resident queries / results */
     int32_t q_groups = 0;
     int64_t q_sources = 0;
@@ -186,6 +195,7 @@ struct msbfs_handle {
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
     int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */
+    int opt_lane_major = -1;                   /* sparse per-group engine: -1 = when every row has <= 16 entries, 0 = never, 1 = whenever the graph allows */
     int opt_count_missing = 1;                 /* after dense bottom-up levels count what lanes still miss instead of the new frontier */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */
@@ -208,6 +218,16 @@ void msbfs_release_graph(msbfs_handle* h);
 /* api.cu: pieces of the loader that comm.cu's sharded load reuses */
 int msbfs_open_graph_file(const char* path, int* fd_out, int32_t* n_out, int64_t* m_out);
 int msbfs_stage_records(msbfs_handle* h, int fd, int64_t first, int64_t count, char* d_dst, const char* what);
+
+/* lane_major.cu */
+struct msbfs_lm_result {
+    int overflow = 0, levels = 0, log_pos_in = 0, log_pos_out = 0;
+    int64_t expanded = 0, scanned = 0, fresh = 0;
+    unsigned long long reach[MSBFS_MAX_LANES];
+};
+int msbfs_lm_ensure(msbfs_handle* h, int lanes);
+int msbfs_lm_run_batch(msbfs_handle* h, int group_base, int lanes, msbfs_lm_result* out);
+void msbfs_lm_release(msbfs_handle* h);
 
 /* traverse.cu */
 int msbfs_traverse(msbfs_handle* h);

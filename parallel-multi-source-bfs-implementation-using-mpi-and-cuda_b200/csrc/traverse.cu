@@ -1205,6 +1205,16 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
             streak_grid = per_sm * h->sm_count;
     }
 
+    /* road-like graph: the sparse per-group engine (lane_major.cu) takes the batches it can hold */
+    bool lm_on = (h->opt_lane_major == 1 || (h->opt_lane_major < 0 && h->max_degree <= 16u)) && h->opt_direction != 2 &&
+                 h->max_degree <= (unsigned)h->opt_streak_max_deg;
+    if (lm_on) {
+        int rc = msbfs_lm_ensure(h, lanes_per_batch);
+        if (rc) return rc;
+        lm_on = h->lm_grid > 0;
+    }
+    h->lm_expanded = h->lm_scanned = h->lm_fresh = 0;
+
     ull* d_reached = nullptr;
     if (want_reached) {
         MSBFS_CUDA(cudaMalloc(&d_reached, sizeof(ull) * MSBFS_MAX_LANES));
@@ -1220,6 +1230,27 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
         L.cur_batch = batches; L.cur_level = -1;
         MsbfsNvtxRange nvtx_batch("msbfs_batch");
         L.mark_batch();
+        if (lm_on) {
+            msbfs_lm_result r;
+            MSBFS_CUDA(cudaMemcpyAsync(&r.log_pos_in, &h->d_ctrl->log_pos, sizeof(int), cudaMemcpyDeviceToHost, s));
+            MSBFS_CUDA(cudaStreamSynchronize(s));
+            int rc = MSBFS_OK;
+            L.timed(SLOT_LANE_MAJOR, [&] { rc = msbfs_lm_run_batch(h, group_base, lanes, &r); });
+            if (rc) return rc;
+            if (!r.overflow) {
+                L.launches += 2; /* inject + store beside the cooperative kernel */
+                MSBFS_CUDA(cudaMemcpyAsync(&h->d_ctrl->log_pos, &r.log_pos_out, sizeof(int), cudaMemcpyHostToDevice, s));
+                MSBFS_CUDA(cudaStreamSynchronize(s));
+                levels += r.levels; levels_td += r.levels;
+                h->lm_expanded += r.expanded; h->lm_scanned += r.scanned; h->lm_fresh += r.fresh;
+                if (want_reached)
+                    for (int j = 0; j < lanes; ++j) (*reached_out)[(size_t)group_base + j] = r.reach[j];
+                L.mark_batch();
+                continue;
+            }
+            /* a level outgrew the queue: this is not a graph for the sparse engine; the batch starts over below */
+            lm_on = false;
+        }
         L.timed(SLOT_OTHER, [&] { init_batch_kernel<<<1, MSBFS_MAX_LANES, 0, s>>>(h->d_ctrl, lanes, (long long)h->nnz, (long long)h->n_active); });
         MSBFS_CUDA(cudaMemsetAsync(h->d_visited, 0, word_bytes, s));
         MSBFS_CUDA(cudaMemsetAsync(h->d_bitmaps, 0, sizeof(unsigned) * 3 * (size_t)nblk, s));
@@ -1422,7 +1453,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
     h->stats.alg_bytes = 0; h->stats.kernel_launches = 0; h->stats.run_ms = 0.0; h->stats.bottom_up_ms = 0.0;
     h->level_log.clear();
     static const char* kSlotNames[MSBFS_NUM_SLOTS] = {"td_heavy", "td_expand_g32", "td_expand_g8", "td_expand_g2",
-                                                      "bu_segment", "(unused)", "(unused)", "bu_thread",
+                                                      "bu_segment", "lane_major", "(unused)", "bu_thread",
                                                       "td_finalize", "bu_heavy_finalize", "count", "bookkeeping"};
     for (int i = 0; i < MSBFS_NUM_SLOTS; ++i) {
         std::memset(&h->slot_profile[i], 0, sizeof h->slot_profile[i]);
@@ -1474,13 +1505,24 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
             p.vertices_examined = (int64_t)hc.k_examined[i]; p.words_written = (int64_t)hc.k_written[i];
             p.alg_bytes = 4ll * p.scanned + w * p.words_fetched + (16ll + w) * p.vertices_examined + 2ll * w * p.words_written;
         }
+        {   /* the lane-major batches keep their own counters */
+            msbfs_kernel_profile& p = h->slot_profile[SLOT_LANE_MAJOR];
+            p.scanned = h->lm_scanned; p.words_fetched = h->lm_scanned; p.vertices_examined = h->lm_expanded; p.words_written = h->lm_fresh;
+            p.alg_bytes = 24ll * p.vertices_examined + 8ll * p.scanned + 16ll * p.words_written;
+        }
         /* filled only when every launch was timed (option "profile") */
-        h->stats.bottom_up_ms = h->slot_profile[SLOT_BU_HEAVY].ms + h->slot_profile[SLOT_BU_G32].ms +
+        h->stats.bottom_up_ms = h->slot_profile[SLOT_BU_HEAVY].ms + h->slot_profile[SLOT_BU_G8].ms +
                                 h->slot_profile[SLOT_BU_G2].ms + h->slot_profile[SLOT_BU_HEAVY_FINALIZE].ms;
     }
     long long bytes = 0;
     for (const LevelLog& l : h->level_log) {
         h->stats.frontier_vertices += (int64_t)l.frontier_vertices;
+        if (l.direction == 3) { /* lane-major level: queue entry 8 B + two row offsets 16 B per visit, col 4 B + bitmap word
+                                   4 B per entry, bitmap update 8 B + queue entry 8 B per newly visited vertex */
+            h->stats.scanned_top_down += (int64_t)l.scanned;
+            bytes += 24ll * (long long)l.vertices_examined + 8ll * (long long)l.scanned + 16ll * (long long)l.words_written;
+            continue;
+        }
         if (l.direction == 1) h->stats.scanned_top_down += (int64_t)l.scanned;
         if (l.direction == 2) { h->stats.scanned_bottom_up += (int64_t)l.scanned; h->stats.candidate_vertices += (int64_t)l.vertices_examined; }
         /* col entry 4 B; every lane word moved (fetched through col, or stored) w B;
@@ -1498,6 +1540,7 @@ int traverse_impl(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_
 } // namespace
 
 void msbfs_release_traversal(msbfs_handle* h) {
+    msbfs_lm_release(h);
     if (h->d_bitmaps && h->stream && h->opt_l2_persist) {
         /* the access-policy window points at memory that is about to be freed */
         cudaStreamAttrValue attr;
