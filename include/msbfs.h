@@ -69,6 +69,8 @@ int msbfs_destroy(msbfs_t* h);
  *                row has at most 16 entries (default), 0 = never, 1 = on any graph whose longest
  *                row fits "streak_max_deg"; a batch whose level outgrows the queue (2 x the
  *                non-isolated vertices) is redone by the bit-parallel engine
+ *   "lm_ell"     1 = the lane-major engine reads rows from fixed-width records (4 or 8 ids per vertex,
+ *                one 16- or 32-byte load) when every row has at most 8 entries (default), 0 = from the CSR
  *   "count_missing"  1 = after a bottom-up level that leaves fewer vertices unfinished than it put
  *                into the frontier, take the per-lane counts from what the unfinished vertices
  *                still miss instead of from the new frontier words (default), 0 = always the latter

@@ -246,6 +246,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "lane_major")) {
         if (value < -1 || value > 1) return msbfs_fail(MSBFS_ERR_INVALID, "lane_major must be -1, 0 or 1");
         h->opt_lane_major = (int)value;
+    } else if (!std::strcmp(key, "lm_ell")) {
+        h->opt_lm_ell = value != 0;
+        msbfs_lm_release(h); /* rebuilt with or without the records at the next run */
     } else if (!std::strcmp(key, "count_missing")) {
         h->opt_count_missing = value != 0;
     } else if (!std::strcmp(key, "col_width")) {

@@ -161,6 +161,8 @@ struct msbfs_handle {
     unsigned int* d_lm_bits = nullptr;
     unsigned long long* d_lm_q[2] = {nullptr, nullptr};
     void* d_lm_ctrl = nullptr;
+    int* d_lm_ell = nullptr;      /* rows as fixed-width records when every row has <= 8 entries */
+    int lm_ell_width = 0;
     int lm_lanes = 0, lm_grid = 0;
     long long lm_cap = 0;
     int64_t lm_expanded = 0, lm_scanned = 0, lm_fresh = 0; /* totals of the last run's lane-major batches */
@@ -196,6 +198,7 @@ struct msbfs_handle {
     int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
     int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */
     int opt_lane_major = -1;                   /* sparse per-group engine: -1 = when every row has <= 16 entries, 0 = never, 1 = whenever the graph allows */
+    int opt_lm_ell = 1;                        /* lane-major engine: fixed-width row records when every row has <= 8 entries */
     int opt_count_missing = 1;                 /* after dense bottom-up levels count what lanes still miss instead of the new frontier */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */
@@ -221,7 +224,7 @@ int msbfs_stage_records(msbfs_handle* h, int fd, int64_t first, int64_t count, c
 
 /* lane_major.cu */
 struct msbfs_lm_result {
-    int overflow = 0, levels = 0, log_pos_in = 0, log_pos_out = 0;
+    int overflow = 0, levels = 0, log_pos_in = 0, log_pos_out = 0, want_reach = 0;
     int64_t expanded = 0, scanned = 0, fresh = 0;
     unsigned long long reach[MSBFS_MAX_LANES];
 };

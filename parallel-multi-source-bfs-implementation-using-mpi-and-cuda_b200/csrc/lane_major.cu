@@ -33,7 +33,13 @@ namespace cg = cooperative_groups;
 namespace {
 
 typedef unsigned long long ull;
-constexpr int LM_CTA = 256;
+#ifndef MSBFS_LM_CTA
+#define MSBFS_LM_CTA 256
+#endif
+constexpr int LM_CTA = MSBFS_LM_CTA;
+#ifndef MSBFS_LM_MINB
+#define MSBFS_LM_MINB 4 /* resident blocks per SM asked of the BFS kernel (register cap) */
+#endif
 
 struct LmCtrl {
     ull tail[2];                       /* entries in queue 0 / 1 */
@@ -98,16 +104,23 @@ __global__ void __launch_bounds__(LM_CTA) lm_inject_kernel(LmCtrl* c, unsigned* 
  * of a ring vertex are already in), an atomicOr only for candidates — and enqueues the ones it
  * set.  Per-group counts of the level live in shared memory; F(group) += (level + 1) x count once
  * per level and block, one global atomicAdd per group and block at the very end. */
-__global__ void __launch_bounds__(LM_CTA) lm_bfs_kernel(LmCtrl* c, unsigned* __restrict__ bits, long long nwords, ull* q0, ull* q1, ull cap,
-                                                        const long long* __restrict__ row_ptr, const int* __restrict__ col, int lanes,
-                                                        int max_degree, LevelLog* log, int log_cap) {
+/* ELL = width of the fixed-width copy of the rows (0: read the CSR).  Road-like graphs have rows of
+ * at most 4 or 8 entries: one 16- or 32-byte record per vertex (-1 padded) replaces two row offsets
+ * and the row, three sectors, by one. */
+template <bool REACH, int ELL>
+__global__ void __launch_bounds__(LM_CTA, MSBFS_LM_MINB) lm_bfs_kernel(LmCtrl* c, unsigned* __restrict__ bits, long long nwords, ull* q0, ull* q1, ull cap,
+                                                        const long long* __restrict__ row_ptr, const int* __restrict__ col,
+                                                        const int* __restrict__ ell, int lanes, int max_degree, LevelLog* log, int log_cap) {
     cg::grid_group grid = cg::this_grid();
     __shared__ unsigned s_cnt[MSBFS_MAX_LANES];   /* newly visited this level, per group */
     __shared__ unsigned s_deg[MSBFS_MAX_LANES];   /* CSR entries of the vertices expanded this level, per group */
     __shared__ ull s_sum[MSBFS_MAX_LANES];
     __shared__ ull s_reach[MSBFS_MAX_LANES];
-    __shared__ int s_warp[LM_CTA / 32];
-    __shared__ ull s_base;
+    __shared__ int s_warp[2][LM_CTA / 32]; /* double-buffered by trip: two barriers per trip instead of three */
+    __shared__ ull s_base[2];
+    __shared__ ull s_lvl;
+    int trip = 0;
+    if (threadIdx.x == 0) s_lvl = 0ull;
     for (int j = threadIdx.x; j < MSBFS_MAX_LANES; j += LM_CTA) { s_cnt[j] = 0u; s_deg[j] = 0u; s_sum[j] = 0ull; s_reach[j] = 0ull; }
     __syncthreads();
     const ull gtid = (ull)blockIdx.x * blockDim.x + threadIdx.x, gsize = (ull)gridDim.x * blockDim.x;
@@ -129,32 +142,57 @@ __global__ void __launch_bounds__(LM_CTA) lm_bfs_kernel(LmCtrl* c, unsigned* __r
         ull* qn = cur ? q0 : q1;
         /* whole blocks iterate together (the queue reservation synchronises the block) */
         const ull rounds = (n + gsize - 1) / gsize;
+        ull lvl_sc = 0;
         for (ull r = 0; r < rounds; ++r) {
             const ull i = r * gsize + gtid;
             const bool on = i < n;
             int lane_id = 0, v = 0;
             long long beg = 0, end = 0;
+            int row[ELL > 0 ? ELL : 1];
+#pragma unroll
+            for (int k = 0; k < (ELL > 0 ? ELL : 1); ++k) row[k] = -1;
             if (on) {
                 const ull e = qc[i];
                 lane_id = (int)(e >> 32);
                 v = (int)(unsigned)e;
-                beg = row_ptr[v];
-                end = row_ptr[v + 1];
+                if (ELL > 0) {
+#pragma unroll
+                    for (int k4 = 0; k4 < ELL / 4; ++k4) {
+                        const int4 r4 = __ldg(reinterpret_cast<const int4*>(ell) + (long long)v * (ELL / 4) + k4);
+                        row[4 * k4] = r4.x; row[4 * k4 + 1] = r4.y; row[4 * k4 + 2] = r4.z; row[4 * k4 + 3] = r4.w;
+                    }
+                    int deg = 0;
+#pragma unroll
+                    for (int k = 0; k < ELL; ++k) deg += row[k] >= 0;
+                    end = deg; /* beg = 0: only the difference is used below */
+                } else {
+                    beg = row_ptr[v];
+                    end = row_ptr[v + 1];
+                }
                 ++expanded;
                 scanned += (ull)(end - beg);
-                atomicAdd(&s_deg[lane_id], (unsigned)(end - beg));
+                lvl_sc += (ull)(end - beg);
+                if (REACH) atomicAdd(&s_deg[lane_id], (unsigned)(end - beg)); /* only the traversed-edges pass needs it per group */
             }
             unsigned* mybits = bits + (long long)lane_id * nwords;
             /* four neighbours per trip; the trip count is the same for the whole block (block_append
              * synchronises), so it comes from the graph's longest row */
-            for (int k0 = 0; k0 < max_degree; k0 += 4) {
+            const int trips_end = ELL > 0 ? ELL : max_degree;
+#pragma unroll
+            for (int k0 = 0; k0 < trips_end; k0 += 4) {
                 int u[4];
                 bool cand[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const long long e = beg + k0 + k;
-                    cand[k] = on && e < end;
-                    u[k] = cand[k] ? __ldg(col + e) : 0;
+                    if (ELL > 0) {
+                        u[k] = row[(k0 + k) < ELL ? (k0 + k) : 0];
+                        cand[k] = on && u[k] >= 0;
+                        if (!cand[k]) u[k] = 0;
+                    } else {
+                        const long long e = beg + k0 + k;
+                        cand[k] = on && e < end;
+                        u[k] = cand[k] ? __ldg(col + e) : 0;
+                    }
                 }
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
@@ -178,16 +216,18 @@ __global__ void __launch_bounds__(LM_CTA) lm_bfs_kernel(LmCtrl* c, unsigned* __r
                     const int t = __shfl_up_sync(0xffffffffu, incl, d);
                     if ((threadIdx.x & 31) >= d) incl += t;
                 }
-                if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
+                const int pb = trip & 1;
+                ++trip;
+                if ((threadIdx.x & 31) == 31) s_warp[pb][threadIdx.x >> 5] = incl;
                 __syncthreads();
                 if (threadIdx.x == 0) {
                     int total = 0;
 #pragma unroll
-                    for (int w = 0; w < LM_CTA / 32; ++w) { const int t = s_warp[w]; s_warp[w] = total; total += t; }
-                    s_base = total ? atomicAdd(&c->tail[cur ^ 1], (ull)total) : 0ull;
+                    for (int w = 0; w < LM_CTA / 32; ++w) { const int t = s_warp[pb][w]; s_warp[pb][w] = total; total += t; }
+                    s_base[pb] = total ? atomicAdd(&c->tail[cur ^ 1], (ull)total) : 0ull;
                 }
                 __syncthreads();
-                ull pos = s_base + (ull)s_warp[threadIdx.x >> 5] + (ull)(incl - mine);
+                ull pos = s_base[pb] + (ull)s_warp[pb][threadIdx.x >> 5] + (ull)(incl - mine);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     if (cand[k]) {
@@ -196,20 +236,18 @@ __global__ void __launch_bounds__(LM_CTA) lm_bfs_kernel(LmCtrl* c, unsigned* __r
                         ++pos;
                     }
                 }
-                __syncthreads(); /* s_warp / s_base are reused by the next trip */
             }
         }
         __syncthreads();
-        ull lvl_sc = 0;
         for (int j = threadIdx.x; j < lanes; j += LM_CTA) {
             s_sum[j] += (ull)(level + 1) * (ull)s_cnt[j];   /* main.cu:81-87, level by level */
-            s_reach[j] += (ull)s_deg[j];
-            lvl_sc += (ull)s_deg[j];
             s_cnt[j] = 0u;
-            s_deg[j] = 0u;
+            if (REACH) { s_reach[j] += (ull)s_deg[j]; s_deg[j] = 0u; }
         }
         for (int d = 16; d > 0; d >>= 1) lvl_sc += __shfl_xor_sync(0xffffffffu, lvl_sc, d);
-        if ((threadIdx.x & 31) == 0 && lvl_sc) atomicAdd(&c->lvl_scanned, lvl_sc);
+        if ((threadIdx.x & 31) == 0 && lvl_sc) atomicAdd(&s_lvl, lvl_sc);
+        __syncthreads();
+        if (threadIdx.x == 0) { if (s_lvl) atomicAdd(&c->lvl_scanned, s_lvl); s_lvl = 0ull; } /* one global atomic per block and level */
         grid.sync(); /* everyone is done reading queue `cur` and appending to the other one */
         if (blockIdx.x == 0 && threadIdx.x == 0) {
             const ull next_n = c->tail[cur ^ 1];
@@ -242,6 +280,16 @@ __global__ void __launch_bounds__(LM_CTA) lm_bfs_kernel(LmCtrl* c, unsigned* __r
     if (blockIdx.x == 0 && threadIdx.x == 0) c->levels = level;
 }
 
+/* CSR rows -> fixed-width records of W ids, -1 padded (every row has at most W entries) */
+__global__ void lm_build_ell_kernel(const long long* __restrict__ row_ptr, const int* __restrict__ col, int n_active, int W,
+                                    int* __restrict__ ell) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n_active * W) return;
+    const int v = (int)(i / W), k = (int)(i % W);
+    const long long e = row_ptr[v] + k;
+    ell[i] = e < row_ptr[v + 1] ? col[e] : -1;
+}
+
 __global__ void lm_store_kernel(const LmCtrl* c, long long* __restrict__ sums, int group_base, int lanes) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < lanes) sums[group_base + j] = (long long)c->sums[j];
@@ -253,6 +301,7 @@ void msbfs_lm_release(msbfs_handle* h) {
     cudaFree(h->d_lm_bits); h->d_lm_bits = nullptr;
     cudaFree(h->d_lm_q[0]); cudaFree(h->d_lm_q[1]); h->d_lm_q[0] = h->d_lm_q[1] = nullptr;
     cudaFree(h->d_lm_ctrl); h->d_lm_ctrl = nullptr;
+    cudaFree(h->d_lm_ell); h->d_lm_ell = nullptr; h->lm_ell_width = 0;
     h->lm_lanes = 0; h->lm_cap = 0; h->lm_grid = 0;
 }
 
@@ -263,7 +312,7 @@ int msbfs_lm_ensure(msbfs_handle* h, int lanes) {
     msbfs_lm_release(h);
     int coop = 0, per_sm = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device);
-    if (!coop || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_bfs_kernel, LM_CTA, 0) != cudaSuccess || per_sm <= 0) {
+    if (!coop || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lm_bfs_kernel<true, 8>, LM_CTA, 0) != cudaSuccess || per_sm <= 0) {
         cudaGetLastError();
         return MSBFS_OK;
     }
@@ -273,6 +322,14 @@ int msbfs_lm_ensure(msbfs_handle* h, int lanes) {
     MSBFS_CUDA(cudaMalloc(&h->d_lm_q[0], sizeof(ull) * cap));
     MSBFS_CUDA(cudaMalloc(&h->d_lm_q[1], sizeof(ull) * cap));
     MSBFS_CUDA(cudaMalloc(&h->d_lm_ctrl, sizeof(LmCtrl)));
+    if (h->opt_lm_ell && h->max_degree <= 8u && h->n_active > 0) {
+        const int W = h->max_degree <= 4u ? 4 : 8;
+        MSBFS_CUDA(cudaMalloc(&h->d_lm_ell, sizeof(int) * (size_t)h->n_active * W));
+        const long long items = (long long)h->n_active * W;
+        lm_build_ell_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(h->d_row_ptr, h->d_col, h->n_active, W, h->d_lm_ell);
+        MSBFS_CUDA(cudaGetLastError());
+        h->lm_ell_width = W;
+    }
     h->lm_lanes = lanes;
     h->lm_cap = (long long)cap;
     h->lm_grid = per_sm * h->sm_count;
@@ -302,8 +359,14 @@ int msbfs_lm_run_batch(msbfs_handle* h, int group_base, int lanes, msbfs_lm_resu
     int log_pos = out->log_pos_in;
     MSBFS_CUDA(cudaMemcpyAsync(&c->log_pos, &log_pos, sizeof(int), cudaMemcpyHostToDevice, s));
     int max_degree = (int)h->max_degree;
-    void* args[] = {&c, &bits, &nwords, &q0, &q1, &cap, &row_ptr, &col, &lanes, &max_degree, &log, &log_cap};
-    const cudaError_t ce = cudaLaunchCooperativeKernel((const void*)lm_bfs_kernel, dim3(h->lm_grid), dim3(LM_CTA), args, 0, s);
+    const int* ell = h->d_lm_ell;
+    void* args[] = {&c, &bits, &nwords, &q0, &q1, &cap, &row_ptr, &col, &ell, &lanes, &max_degree, &log, &log_cap};
+    const void* fn;
+    const bool wr = out->want_reach != 0;
+    if (h->lm_ell_width == 4) fn = wr ? (const void*)lm_bfs_kernel<true, 4> : (const void*)lm_bfs_kernel<false, 4>;
+    else if (h->lm_ell_width == 8) fn = wr ? (const void*)lm_bfs_kernel<true, 8> : (const void*)lm_bfs_kernel<false, 8>;
+    else fn = wr ? (const void*)lm_bfs_kernel<true, 0> : (const void*)lm_bfs_kernel<false, 0>;
+    const cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(h->lm_grid), dim3(LM_CTA), args, 0, s);
     if (ce != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "cooperative launch failed: %s", cudaGetErrorString(ce));
     lm_store_kernel<<<(lanes + 255) / 256, 256, 0, s>>>(c, h->d_sums, group_base, lanes);
     LmCtrl hc;

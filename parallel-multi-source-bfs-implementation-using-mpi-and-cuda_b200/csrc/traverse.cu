@@ -1232,6 +1232,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
         L.mark_batch();
         if (lm_on) {
             msbfs_lm_result r;
+            r.want_reach = want_reached ? 1 : 0;
             MSBFS_CUDA(cudaMemcpyAsync(&r.log_pos_in, &h->d_ctrl->log_pos, sizeof(int), cudaMemcpyDeviceToHost, s));
             MSBFS_CUDA(cudaStreamSynchronize(s));
             int rc = MSBFS_OK;
