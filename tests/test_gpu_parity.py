@@ -23,7 +23,7 @@ def _reset(eng):
     eng.set_option("reorder", 1)
     eng.set_option("lanes", 0)
     eng.set_option("direction", 0)
-    eng.set_option("alpha", 8)
+    eng.set_option("alpha", 40)
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -216,6 +216,47 @@ def test_full_size_config2_properties(pkg, ob, engine):
     o3 = (np.arange(len(pick) + 1) * s).astype(np.int64)
     want = ob.run(n, uv, o3, src.reshape(k, s)[pick].ravel())
     assert np.array_equal(base[pick], want.sums)
+
+
+def test_lane_major_engine_and_its_fallback(pkg, ob, engine):
+    """Road-like graphs run on the second engine (csrc/lane_major.cu: a visited bitmap per group, a
+    queue of (group, vertex) pairs).  Same sums as the oracle and as the bit-parallel engine, with and
+    without the fixed-width row records, the traversed-edges pass included; and on a graph whose
+    frontiers outgrow the queue the batch is handed back to the bit-parallel engine."""
+    def slots(eng):
+        return {p["name"]: p["launches"] for p in eng.kernel_profiles()}
+
+    try:
+        # ---- lattice (rows <= 4 entries) and a path (rows <= 2, 3000 levels), ragged groups with bad ids
+        path_uv = np.stack([np.arange(2999), np.arange(1, 3000)], axis=1).astype(np.int32)
+        for n, uv, k in ((64 * 50, pkg.gen_edges_host(pkg.GEN_LATTICE, 64, 50, pkg.lattice_num_edges(64, 50), 5), 130),
+                         (3000, path_uv, 70)):
+            offs, src = _ragged_queries(np.random.default_rng(n), n, k, 3)
+            want = ob.run(n, uv, offs, src)
+            engine.set_graph_edges(n, uv)
+            for lane_major, ell in ((-1, 1), (1, 0), (0, 1)):
+                engine.set_option("lane_major", lane_major)
+                engine.set_option("lm_ell", ell)
+                assert np.array_equal(engine.run(offs, src), want.sums), (n, lane_major, ell)
+                assert (slots(engine)["lane_major"] > 0) == (lane_major != 0)
+                engine.upload_queries(offs, src)
+                assert np.array_equal(engine.reached_entries(), want.reached_entries), (n, lane_major, ell)
+        # ---- sparse random graph, rows <= 16 entries but exploding frontiers: the queue (2 x the non-isolated
+        #      vertices, at least 65,536 entries) overflows and the bit-parallel engine redoes the batch
+        n, m = 60000, 150000
+        uv = pkg.gen_edges_host(pkg.GEN_ER, n, 0, m, 9)
+        offs, src = pkg.gen_queries_host(n, 96, 3, 4)
+        want = ob.run(n, uv, offs, src)
+        engine.set_option("lane_major", 1)
+        engine.set_option("streak_max_deg", 256)
+        engine.set_graph_edges(n, uv)
+        assert np.array_equal(engine.run(offs, src), want.sums)
+        got = slots(engine)
+        assert got["lane_major"] >= 1 and got["count"] > 0, got   # tried, overflowed, redone by the other engine
+    finally:
+        _reset(engine)
+        engine.set_option("lane_major", -1)
+        engine.set_option("lm_ell", 1)
 
 
 def test_level_log_and_kernel_profiles(pkg, ob, expected, engine):

@@ -54,7 +54,7 @@ def _spread_sample(order, per_part, lanes=512):
 
 
 def _reset(engine):
-    for key, val in (("lanes", 0), ("direction", 0), ("reorder", 1)):
+    for key, val in (("lanes", 0), ("direction", 0), ("reorder", 1), ("lane_major", -1), ("lm_ell", 1)):
         engine.set_option(key, val)
 
 
@@ -107,9 +107,10 @@ def test_config3_kron26_full_size(pkg, ob, engine):
 
 
 def test_config4_lattice4096_full_size(pkg, ob, engine):
-    """4096 x 4096 lattice, 512 groups x 4 sources (thousands of levels, persistent kernel)."""
+    """4096 x 4096 lattice, 512 groups x 4 sources (thousands of levels): the lane-major engine by default,
+    the bit-parallel engine's persistent top-down kernel with lane_major = 0 on the slice."""
     _check_config(pkg, ob, engine, pkg.GEN_LATTICE, 4096, 4096, 2 * 4096 * 4095, 512, 4, per_part=176, slice_groups=128,
-                  slice_checks=[("lanes", 64), ("reorder", 0)])
+                  slice_checks=[("lanes", 64), ("reorder", 0), ("lane_major", 0), ("lm_ell", 0)])
 
 
 def test_config5_er24_full_size(pkg, ob, engine):
