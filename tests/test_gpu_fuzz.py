@@ -60,12 +60,12 @@ def _queries(rng, n):
 def test_random_cases_match_the_oracle(pkg, ob, shape):
     rng = np.random.default_rng(sum(map(ord, shape)))
     with pkg.Engine(0) as eng:
-        for case in range(12):
+        for case in range(40):
             n, uv = _graph(pkg, rng, shape)
             offs, src = _queries(rng, n)
             want = ob.run(n, uv, offs, src)
             eng.set_graph_edges(n, uv)
-            for trial in range(3):
+            for trial in range(4):
                 cfg = {k: (v[int(rng.integers(0, len(v)))] if trial else DEFAULTS[k]) for k, v in OPTIONS.items()}
                 for k, v in cfg.items():
                     eng.set_option(k, v)
