@@ -231,9 +231,11 @@ int msbfs_load_graph_file_sharded(msbfs_t* h, const char* path, void* nccl_comm,
  * 0..R-1, R-1..0, ...  Outputs: order_out[i] = group at run position i (all groups);
  * owner_out[g] = rank that runs group g; *lanes_out = batch width the ranks should set with
  * msbfs_set_option("lanes") (0 = the engine's own choice, when world == 1).  A rank runs its
- * groups in the relative order of order_out.  lanes = 0 lets msbfs_plan_lanes choose: 512,
- * or 256 when that leaves a rank fewer than two batches, halved further while ranks would
- * stay idle.  Host-only; every rank computes the same plan from the same inputs. */
+ * groups in the relative order of order_out.  lanes = 0 chooses: 512; 256 when that leaves a
+ * rank fewer than two batches and the 512-group batches' weights differ by more than 3 x
+ * (power-law graphs: a rank then mixes a fast and a slow batch; hub-less graphs keep 512);
+ * halved further while ranks would stay idle.  msbfs_plan_lanes is the same rule without the
+ * weights (a sizing hint before the graph is loaded).  Host-only; every rank computes the same plan from the same inputs. */
 int msbfs_plan_lanes(int32_t num_groups, int32_t world);
 int msbfs_plan_shares(int32_t num_groups, const int64_t* weights, int32_t world, int32_t lanes,
                       const double* batch_cost, int32_t num_costs, int32_t* order_out, int32_t* owner_out,

@@ -12,7 +12,8 @@
  * levels at the same depth let the bottom-up kernels stop early for the whole batch.  The
  * cost of a batch is dominated by the lane-count-independent scan of the CSR, so batches are
  * as wide as the hardware word allows (512) unless that would leave a rank with fewer than
- * two batches to balance with (then 256), or without any (then halved down to 64).  Batches
+ * two batches to balance with AND the batches' weights differ by more than 3 x (then 256), or
+ * a rank without any batch (then halved down to 64).  Batches
  * are handed to the ranks
  *   - by measured cost when the caller has one (`batch_cost`, e.g. msbfs_get_batch_ms of a
  *     previous pass over the same plan): longest batch first, each to the rank with the
@@ -48,7 +49,24 @@ extern "C" int msbfs_plan_shares(int32_t num_groups, const int64_t* weights, int
     std::vector<int32_t> order((size_t)K);
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) { return weights[x] > weights[y]; });
-    const int plan_lanes = lanes ? lanes : msbfs_plan_lanes(K, world);
+    int plan_lanes = lanes ? lanes : msbfs_plan_lanes(K, world);
+    if (!lanes && plan_lanes == 256 && ((int64_t)K + 511) / 512 >= world) {
+        /* One 512-lane batch per rank costs less than two 256-lane ones (the scan of the CSR is paid per
+         * batch) — unless the batches differ so much in cost that a rank needs two of them to mix a
+         * fast one with a slow one.  The weights tell: on a graph without hubs (Erdos-Renyi: 2 GPUs
+         * 40.9 ms with 2 x 256 lanes per rank, 28 ms with 1 x 512) every 512-group batch weighs the
+         * same; on a power-law graph the first weighs orders of magnitude more than the last. */
+        const int nb512 = (K + 511) / 512;
+        long double lo = -1, hi = 0;
+        for (int b = 0; b < nb512; ++b) {
+            long double w = 0;
+            for (int i = b * 512; i < std::min(K, (b + 1) * 512); ++i) w += (long double)weights[order[(size_t)i]];
+            if (b == nb512 - 1 && K % 512) w *= 512.0L / (K % 512); /* a partial last batch, scaled up */
+            if (lo < 0 || w < lo) lo = w;
+            if (w > hi) hi = w;
+        }
+        if (hi <= 3 * lo) plan_lanes = 512;
+    }
     if (lanes_out) *lanes_out = plan_lanes;
     for (int i = 0; i < K; ++i) order_out[i] = order[(size_t)i];
     if (world == 1 || K == 0) {

@@ -138,7 +138,7 @@ int main(int argc, char* argv[]) {
     /* the traversal state is sized at graph load: say how wide this rank's batches will be */
     {
         const int lanes = msbfs_plan_lanes(K, world_size);
-        if (lanes > 0) msbfs_set_option(eng, "lanes", lanes);
+        if (lanes > 0) msbfs_set_option(eng, "lanes", lanes >= 256 ? 512 : lanes); /* the plan may still widen 256 to 512 */
         else msbfs_set_option(eng, "expect_groups", K);
     }
     if (nccl_in_window) nccl_setup();

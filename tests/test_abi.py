@@ -180,6 +180,11 @@ def test_share_planning_and_explicit_id_packing(pkg, ob):
     snake, _ = pkg.plan_shares(costs, 8, lanes=256)
     loads_snake = [sum(measured[g // 256] for g in sh[::256].tolist()) for sh in snake]
     assert max(loads) <= max(loads_snake) and max(loads) < 1.15 * sum(measured) / 8
+    # one batch per rank: 512 lanes when the batches weigh about the same (no hubs), 256 when they do not
+    flat = 1000 + (np.arange(4096) % 7).astype(np.int64)
+    assert pkg.plan_shares(flat, 8)[1] == 512 and pkg.plan_shares(flat, 2)[1] == 512
+    skewed = (np.arange(4096, 0, -1).astype(np.int64)) ** 3
+    assert pkg.plan_shares(skewed, 8)[1] == 256 and pkg.plan_shares(skewed, 4)[1] == 512  # two batches per rank at 4
     assert pkg.lib().msbfs_plan_lanes(4096, 1) == 0 and pkg.lib().msbfs_plan_lanes(4096, 8) == 256
     assert pkg.lib().msbfs_plan_lanes(4096, 2) == 512 and pkg.lib().msbfs_plan_lanes(100, 8) == 64
     offs = np.array([0, 2, 2, 5, 6], dtype=np.int64)
