@@ -481,6 +481,46 @@ def run_ours(args, wl, rank, local_rank, world):
     #      batch order) go back into msbfs_plan_shares, which hands the batches out longest first
     #      to the least-loaded rank instead of in snake order
     plan_note = "one rank" if world == 1 else ("contiguous file order" if args.contiguous else "snake order")
+
+    def adopt(new_share, lanes_opt):
+        nonlocal share, mine, my_offs, my_src, lo, hi, h2d_bytes, d2h_bytes
+        share = new_share
+        mine = share[rank].astype(np.int64)
+        my_offs, my_src = pkg.gather_groups(offs, src, mine)
+        lo, hi = 0, int(mine.size)
+        h2d_bytes = int(my_offs.nbytes + my_src.nbytes)
+        d2h_bytes = int(mine.size * 8)
+        if lanes_opt:
+            eng.set_option("lanes", lanes_opt)
+        eng.upload_queries(my_offs, my_src)
+
+    def warm_max_ms(n=2):
+        out = 0.0
+        for _ in range(n):
+            flush_buf.zero_()
+            out = reduce_max(one_step_resident()[0])
+        return out
+
+    # ---- batch width by measurement: when 512-group batches would leave every rank exactly one, the
+    #      static rule picks 256 on skewed weights (a rank then mixes a fast and a slow batch).  Whether
+    #      that pays depends on the graph (Kronecker-26 at 8 GPUs: yes, by 10 %; RMAT-22 at 2: no, by
+    #      30 %), so the other width gets two warm-up steps too and the faster plan is kept.
+    width_note = ""
+    if (world > 1 and not args.contiguous and not args.no_replan and not args.lanes and plan_lanes == 256
+            and (K + 511) // 512 >= world):
+        t256 = warm_max_ms(1)
+        share256 = share
+        share512, _ = pkg.plan_shares(costs, world, lanes=512)
+        adopt(share512, 512)
+        t512 = warm_max_ms(2)
+        if t512 <= t256:
+            plan_lanes = 512
+            width_note = f"; 512-lane batches measured faster than 256 ({t512:.1f} vs {t256:.1f} ms)"
+        else:
+            adopt(share256, 256)
+            warm_max_ms(1)
+            width_note = f"; 256-lane batches measured faster than 512 ({t256:.1f} vs {t512:.1f} ms)"
+
     if world > 1 and not args.contiguous and not args.no_replan:
         mine_ms = eng.batch_ms() if hi > lo else []
         all_ms = [None] * world
@@ -506,13 +546,7 @@ def run_ours(args, wl, rank, local_rank, world):
             owner2[share2[r]] = r
         loads_new = [sum(c for b, c in enumerate(cost_b) if int(owner2[run_order[b * width]]) == r) for r in range(world)]
         if max(loads_new) < 0.98 * max(loads_old):
-            share = share2
-            mine = share[rank].astype(np.int64)
-            my_offs, my_src = pkg.gather_groups(offs, src, mine)
-            lo, hi = 0, int(mine.size)
-            h2d_bytes = int(my_offs.nbytes + my_src.nbytes)
-            d2h_bytes = int(mine.size * 8)
-            eng.upload_queries(my_offs, my_src)
+            adopt(share2, 0)
             flush_buf.zero_()
             one_step_resident()  # the new share's own warm-up
             plan_note = (f"longest batch first onto the least-loaded rank, from the warm-up's per-batch times "
@@ -520,6 +554,7 @@ def run_ours(args, wl, rank, local_rank, world):
         else:
             plan_note = f"snake order (measured-cost plan no better: {max(loads_new):.1f} vs {max(loads_old):.1f} ms)"
         del order_all
+        plan_note += width_note
 
     # ---- timed steps: device time (events) per step, max over ranks; wall as a cross-check
     sampler = ClockSampler(local_rank)
