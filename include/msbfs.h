@@ -71,6 +71,8 @@ int msbfs_destroy(msbfs_t* h);
  *                non-isolated vertices) is redone by the bit-parallel engine
  *   "lm_ell"     1 = the lane-major engine reads rows from fixed-width records (4 or 8 ids per vertex,
  *                one 16- or 32-byte load) when every row has at most 8 entries (default), 0 = from the CSR
+ *   "stage_threads"  host threads that fill the loader's pinned staging buffers, 1 ... 16; 0 = 4 below
+ *                1 GiB, 8 from there on, never more than half the cores (default)
  *   "count_missing"  1 = after a bottom-up level that leaves fewer vertices unfinished than it put
  *                into the frontier, take the per-lane counts from what the unfinished vertices
  *                still miss instead of from the new frontier words (default), 0 = always the latter

@@ -19,7 +19,8 @@
 namespace {
 
 constexpr size_t STAGE_BYTES = 16u << 20; /* one pinned staging buffer */
-constexpr int STAGE_THREADS = 4;          /* filler threads, two buffers each */
+constexpr int STAGE_THREADS = 4;          /* filler threads (two buffers each) for loads below 1 GiB */
+constexpr int STAGE_THREADS_MAX = 16;
 
 /* Pinned staging pipeline: STAGE_THREADS host threads fill pinned buffers (pread from the
  * file, or memcpy from the caller's pageable array) and queue asynchronous H2D copies on
@@ -46,7 +47,12 @@ template <class Fill>
 int staged_upload(msbfs_handle* h, char* d_dst, size_t total, Fill fill, const char* what) {
     if (total == 0) return MSBFS_OK;
     const size_t nchunks = (total + STAGE_BYTES - 1) / STAGE_BYTES;
-    const int nthreads = (int)std::min<size_t>(STAGE_THREADS, nchunks);
+    /* one thread copies ~4 GB/s out of the page cache: four keep up with a small file, a multi-GiB
+     * one wants more (option "stage_threads"; by default 8 from 1 GiB on, capped by the cores) */
+    int want = h->opt_stage_threads > 0 ? h->opt_stage_threads : (total >= ((size_t)1 << 30) ? 8 : STAGE_THREADS);
+    const unsigned cores = std::thread::hardware_concurrency();
+    if (h->opt_stage_threads == 0 && cores > 0) want = std::min<int>(want, std::max(2u, cores / 2));
+    const int nthreads = (int)std::min<size_t>((size_t)std::min(want, STAGE_THREADS_MAX), nchunks);
     /* only the buffers this upload will use, and no larger than it needs: pinning memory costs
      * milliseconds per buffer, which is most of the preprocessing window of a small graph */
     const size_t one = nchunks == 1 ? ((total + 4095) / 4096) * 4096 : STAGE_BYTES;
@@ -249,6 +255,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "lm_ell")) {
         h->opt_lm_ell = value != 0;
         msbfs_lm_release(h); /* rebuilt with or without the records at the next run */
+    } else if (!std::strcmp(key, "stage_threads")) {
+        if (value < 0 || value > STAGE_THREADS_MAX) return msbfs_fail(MSBFS_ERR_INVALID, "stage_threads out of range [0, 16]");
+        h->opt_stage_threads = (int)value;
     } else if (!std::strcmp(key, "count_missing")) {
         h->opt_count_missing = value != 0;
     } else if (!std::strcmp(key, "col_width")) {

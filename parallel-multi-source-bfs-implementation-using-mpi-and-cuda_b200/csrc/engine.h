@@ -184,9 +184,9 @@ struct msbfs_handle {
     unsigned long long* d_scalar = nullptr; /* 8-byte scratch for the packed min all-reduce */
 
     /* pinned staging buffers of the loader (api.cu), allocated on first use */
-    char* stage_buf[8] = {};
-    size_t stage_cap[8] = {};
-    cudaEvent_t stage_ev[8] = {};
+    char* stage_buf[32] = {};   /* two per filler thread */
+    size_t stage_cap[32] = {};
+    cudaEvent_t stage_ev[32] = {};
 
     /* options */
     int opt_lanes = 0, opt_direction = 0, opt_l2_persist = 1;
@@ -199,6 +199,7 @@ struct msbfs_handle {
     int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */
     int opt_lane_major = -1;                   /* sparse per-group engine: -1 = when every row has <= 16 entries, 0 = never, 1 = whenever the graph allows */
     int opt_lm_ell = 1;                        /* lane-major engine: fixed-width row records when every row has <= 8 entries */
+    int opt_stage_threads = 0;                 /* host threads filling the loader's pinned staging buffers; 0 = by size of the load */
     int opt_count_missing = 1;                 /* after dense bottom-up levels count what lanes still miss instead of the new frontier */
     int opt_seg = 0;                           /* bottom-up segment length (next graph load); 0 = by graph size */
     int opt_col_width = 0;                     /* col entries per load in the bottom-up scan: 4 (128-bit), 8 (256-bit), 0 = 8 for the long-row kernel at 512 lanes, else 4 */

@@ -17,8 +17,14 @@ path = "/dev/shm/msbfs_loader_bench.bin"
 pkg.write_graph_file(path, n, uv)
 size_gb = os.path.getsize(path) / 1e9
 with pkg.Engine(0) as eng:
+    def with_threads(t):
+        eng.set_option("stage_threads", t)
+        eng.load_graph_file(path)
     for label, fn in [("load_graph_file (/dev/shm)", lambda: eng.load_graph_file(path)),
                       ("load_graph_file again", lambda: eng.load_graph_file(path)),
+                      ("  stage_threads=2", lambda: with_threads(2)), ("  stage_threads=4", lambda: with_threads(4)),
+                      ("  stage_threads=8", lambda: with_threads(8)), ("  stage_threads=12", lambda: with_threads(12)),
+                      ("  stage_threads=16", lambda: with_threads(16)), ("  stage_threads=0 (default)", lambda: with_threads(0)),
                       ("set_graph_edges (host array)", lambda: eng.set_graph_edges(n, uv)),
                       ("set_graph_edges_device", lambda: eng.set_graph_edges_device(n, m, buf.data_ptr()))]:
         t0 = time.time(); fn(); dt = time.time() - t0
