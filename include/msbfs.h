@@ -73,6 +73,9 @@ int msbfs_destroy(msbfs_t* h);
  *                one 16- or 32-byte load) when every row has at most 8 entries (default), 0 = from the CSR
  *   "stage_threads"  host threads that fill the loader's pinned staging buffers, 1 ... 16; 0 = 4 below
  *                1 GiB, 8 from there on, never more than half the cores (default)
+ *   "tail"       1 = once at most 2^18 vertices (2^23 CSR entries, rows <= 4096) are left unfinished, list them
+ *                and run every remaining level bottom-up over the list in one persistent kernel — on graphs of
+ *                a million vertices or more (default); 2 = on any graph; 0 = never
  *   "count_missing"  1 = after a bottom-up level that leaves fewer vertices unfinished than it put
  *                into the frontier, take the per-lane counts from what the unfinished vertices
  *                still miss instead of from the new frontier words (default), 0 = always the latter

@@ -258,6 +258,9 @@ extern "C" int msbfs_set_option(msbfs_t* h, const char* key, int64_t value) {
     } else if (!std::strcmp(key, "stage_threads")) {
         if (value < 0 || value > STAGE_THREADS_MAX) return msbfs_fail(MSBFS_ERR_INVALID, "stage_threads out of range [0, 16]");
         h->opt_stage_threads = (int)value;
+    } else if (!std::strcmp(key, "tail")) {
+        if (value < 0 || value > 2) return msbfs_fail(MSBFS_ERR_INVALID, "tail must be 0, 1 or 2");
+        h->opt_tail = (int)value;
     } else if (!std::strcmp(key, "count_missing")) {
         h->opt_count_missing = value != 0;
     } else if (!std::strcmp(key, "col_width")) {

@@ -91,6 +91,7 @@ struct LevelVerdict {
     int32_t streak_levels;  /* levels run by the last persistent top-down kernel */
     uint64_t n_f, m_f;
     int64_t m_u;
+    int64_t n_u;            /* vertices some lane still misses */
 };
 
 struct TravArgs {
@@ -155,6 +156,7 @@ struct msbfs_handle {
     LevelLog* d_log = nullptr;
     int log_cap = 0;
     LevelVerdict* h_verdict = nullptr; /* pinned */
+    int* d_tail_list = nullptr;        /* unfinished vertices for the tail kernel + 4 ints of control in front */
 
     /* lane-major engine for road-like graphs (lane_major.cu): a visited bitmap per group, two
      * queues of (group, vertex) pairs, a control block */
@@ -194,6 +196,7 @@ struct msbfs_handle {
     int opt_streak_levels = 1 << 20;           /* cap on levels per persistent launch (profiling) */
     int opt_streak_max_deg = 256;              /* longest row for which the persistent kernel is used */
     int opt_reorder = 1;                       /* run groups heaviest-first (by their sources' degrees) */
+    int opt_tail = 1;                          /* last levels (few unfinished vertices) in one persistent bottom-up kernel over their list */
     int opt_streak = 1;                        /* persistent top-down kernel on short-row graphs  */
     int opt_expect_groups = 0;                 /* most groups a run will carry (sizes the traversal state at graph load); 0 = any */
     int opt_order_key = 0;                     /* run-order key: 0 = two-hop weight of the sources, 1 = smallest source id (spatial proxy) */

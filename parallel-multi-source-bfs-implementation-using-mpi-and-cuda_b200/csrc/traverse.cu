@@ -911,7 +911,7 @@ __device__ __forceinline__ void epilogue_body(LevelCtrl* c, LevelLog* log, int l
         c->log_pos += 1;
         verdict->done = (nf == 0ull);
         verdict->next_direction = next;
-        verdict->n_f = nf; verdict->m_f = mf; verdict->m_u = mu;
+        verdict->n_f = nf; verdict->m_f = mf; verdict->m_u = mu; verdict->n_u = nu;
         verdict->heavy_frontier = (int)c->heavy_frontier;
         c->last_done = (nf == 0ull);
         c->last_next = next;
@@ -1092,6 +1092,111 @@ __global__ void __launch_bounds__(CTA, (NW == 8) ? 2 : 4) td_streak_kernel(TravA
     }
 }
 
+/* ------------------------------------------------ the last levels (tail) --- */
+
+/* After the dense levels a batch is left with a few ten thousand vertices that some lane still
+ * misses (those outside the giant component, mostly) and three or four more levels to run, each of
+ * which would sweep every bitmap and cost launches, a count pass and a host round trip for a
+ * handful of frontier vertices.  Instead the unfinished vertices are listed once and ONE
+ * cooperative kernel runs the remaining levels bottom-up over that list: scan, per-lane counts in
+ * shared memory, epilogue by block 0, two grid barriers per level. */
+constexpr int TAIL_CAP = 1 << 18;           /* most vertices the list may hold */
+constexpr long long TAIL_MAX_ENTRIES = 1ll << 23; /* most CSR entries they may have between them */
+constexpr int TAIL_MAX_ROW = 4096;          /* longest row a single thread is asked to scan */
+
+/* list[0] = count, list[1] = longest row among them, list[4 ...] = the vertices */
+__global__ void __launch_bounds__(CTA) tail_list_kernel(TravArgs a, int nblk, int* __restrict__ list) {
+    const int lane = threadIdx.x & 31;
+    for (int b = global_warp(); b < nblk; b += total_warps()) {
+        const unsigned w = ~a.vis_full[b];
+        const int v = (b << 5) + lane;
+        const bool on = ((w >> lane) & 1u) && v < a.n_active;
+        const unsigned m = __ballot_sync(0xffffffffu, on);
+        if (m == 0u) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&list[0], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (on) {
+            const int pos = base + __popc(m & ((1u << lane) - 1u));
+            if (pos < TAIL_CAP) list[4 + pos] = v;
+            const long long deg = a.row_ptr[v + 1] - a.row_ptr[v];
+            atomicMax(&list[1], (int)min(deg, (long long)0x7fffffff));
+        }
+    }
+}
+
+template <int NW>
+__global__ void __launch_bounds__(CTA, (NW == 8) ? 2 : 4) tail_levels_kernel(TravArgs a, const int* __restrict__ list, int nlist, LevelLog* log,
+                                                                             int log_cap, LevelVerdict* verdict, long long alpha, int max_levels) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ unsigned s_cnt[64 * NW];
+    const int lane = threadIdx.x & 31;
+    const int nblk = a.n_pad >> 5;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    const LW<NW> active = lw_from<NW>(a.ctrl->active);
+    int levels_run = 0;
+    for (;;) {
+        for (int i = threadIdx.x; i < 64 * NW; i += CTA) s_cnt[i] = 0u;
+        __syncthreads();
+        const LW<NW> live = lw_load_volatile<NW>(a.ctrl->live, 0); /* rewritten by the epilogue every level */
+        unsigned scanned = 0, fetched = 0, examined = 0, written = 0;
+        ull full_acc = 0, nf = 0, mf = 0;
+        for (int i = gtid; i < nlist; i += gsize) {
+            const int u = list[i];
+            if (test_bit(a.vis_full, u)) continue;
+            const LW<NW> vis = lw_load<NW>(a.visited, u);
+            const LW<NW> need = lw_andn(live, vis);
+            if (!lw_any(need)) continue;
+            ++examined;
+            const long long beg = a.row_ptr[u], end = a.row_ptr[u + 1];
+            const LW<NW> acc = bu_scan_row<NW, 4>(a, beg, end, need, scanned, fetched);
+            const LW<NW> found = lw_and(acc, need);
+            if (!lw_any(found)) continue;
+            const LW<NW> nv = lw_or(vis, found);
+            lw_store<NW>(a.visited, u, nv);
+            lw_store<NW>(a.nxt, u, found);
+            atomicOr(&a.nxt_nz[u >> 5], 1u << (u & 31));
+            ++written; ++nf; mf += (ull)(end - beg);
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                ull bits = found.w[w];
+                while (bits) {
+                    const int j = __ffsll((long long)bits) - 1;
+                    bits &= bits - 1ull;
+                    atomicAdd(&s_cnt[w * 64 + j], 1u);
+                }
+            }
+            if (lw_covers(nv, active)) {
+                note_full(full_acc, end - beg);
+                atomicOr(&a.vis_full[u >> 5], 1u << (u & 31));
+            }
+        }
+        flush_counters(a.ctrl, SLOT_BU_G2, scanned, fetched, examined, written);
+        flush_full(a.ctrl, full_acc, lane);
+        flush_frontier_totals(a.ctrl, nf, mf, 0u, lane);
+        __syncthreads();
+        for (int i = threadIdx.x; i < 64 * NW; i += CTA)
+            if (s_cnt[i]) atomicAdd(&a.ctrl->cnt[i], (ull)s_cnt[i]);
+        __threadfence();
+        grid.sync();
+        /* the frontier just read becomes the next level's output bitmap: wipe it (everyone is done probing it) */
+        for (int b = gtid; b < nblk; b += gsize) a.cur_nz[b] = 0u;
+        if (blockIdx.x == 0) epilogue_body(a.ctrl, log, log_cap, verdict, 2, alpha, 2);
+        __threadfence();
+        grid.sync();
+        ++levels_run;
+        const volatile LevelCtrl* vc = a.ctrl;
+        const bool stop = vc->last_done || levels_run >= max_levels;
+        ull* t = a.cur; a.cur = a.nxt; a.nxt = t;
+        unsigned* tb = a.cur_nz; a.cur_nz = a.nxt_nz; a.nxt_nz = tb;
+        if (stop) break;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        verdict->streak_levels = levels_run;
+        __threadfence_system();
+    }
+}
+
 __global__ void store_sums_kernel(const LevelCtrl* c, long long* __restrict__ sums, int group_base, int lanes) {
     const int j = threadIdx.x;
     if (j < lanes) sums[group_base + j] = (long long)c->sums[j];
@@ -1215,6 +1320,19 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
     }
     h->lm_expanded = h->lm_scanned = h->lm_fresh = 0;
 
+    /* the tail kernel: cooperative, one block per SM is plenty for a list of at most 2^18 vertices */
+    int tail_grid = 0;
+    /* (worth it from about a million vertices on: below that a level's sweeps and launches cost less than
+     * listing the vertices — RMAT-16 0.81 -> 0.93 ms with it, Kronecker-26 133.4 -> 129.3) */
+    if (h->opt_tail && h->opt_direction != 1 && (h->opt_tail > 1 || h->n_pad >= (1 << 20))) {
+        int coop = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device);
+        if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tail_levels_kernel<NW>, CTA, 0) == cudaSuccess && per_sm > 0)
+            tail_grid = h->sm_count;
+        else cudaGetLastError();
+        if (tail_grid > 0 && !h->d_tail_list) MSBFS_CUDA(cudaMalloc(&h->d_tail_list, sizeof(int) * (size_t)(TAIL_CAP + 4)));
+    }
+
     ull* d_reached = nullptr;
     if (want_reached) {
         MSBFS_CUDA(cudaMalloc(&d_reached, sizeof(ull) * MSBFS_MAX_LANES));
@@ -1223,6 +1341,7 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
 
     MSBFS_CUDA(cudaMemsetAsync(h->d_ctrl, 0, sizeof(LevelCtrl), s)); /* log_pos and the per-kernel accumulators */
     int batches = 0;
+    int tail_n = 0;
     long long levels = 0, levels_td = 0, levels_bu = 0;
 
     for (int group_base = 0; group_base < K; group_base += lanes_per_batch, ++batches) {
@@ -1316,6 +1435,34 @@ int run_batches(msbfs_handle* h, bool want_reached, std::vector<ull>* reached_ou
                         td_expand_kernel<NW, 2, 4><<<L.grid_for_warps(a.blk_end - a.blk_g8), CTA, 0, s>>>(a, a.blk_g8, a.blk_end);
                     });
                 L.timed(SLOT_TD_FINALIZE, [&] { td_finalize_kernel<NW><<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk); });
+            } else if (tail_grid > 0 && h->h_verdict->n_u > 0 && h->h_verdict->n_u <= TAIL_CAP && h->h_verdict->m_u <= TAIL_MAX_ENTRIES &&
+                       [&] { /* list the unfinished vertices; usable when they fit and none of them has a long row */
+                           int head[4] = {0, 0, 0, 0};
+                           if (cudaMemsetAsync(h->d_tail_list, 0, sizeof head, s) != cudaSuccess) return false;
+                           L.timed(SLOT_OTHER, [&] { tail_list_kernel<<<L.grid_for_warps(nblk), CTA, 0, s>>>(a, nblk, h->d_tail_list); });
+                           if (cudaMemcpyAsync(head, h->d_tail_list, sizeof head, cudaMemcpyDeviceToHost, s) != cudaSuccess) return false;
+                           if (cudaStreamSynchronize(s) != cudaSuccess) return false;
+                           tail_n = head[0];
+                           return head[0] > 0 && head[0] <= TAIL_CAP && head[1] <= TAIL_MAX_ROW;
+                       }()) {
+                /* every remaining level in one launch */
+                MSBFS_CUDA(cudaMemsetAsync(a.nxt_nz, 0, sizeof(unsigned) * (size_t)nblk, s));
+                long long alpha = h->opt_alpha;
+                int max_levels = 1 << 20;
+                const int* list = h->d_tail_list + 4;
+                void* args[] = {&a, &list, &tail_n, &h->d_log, &h->log_cap, &h->h_verdict, &alpha, &max_levels};
+                cudaError_t ce = cudaSuccess;
+                L.timed(SLOT_BU_G2, [&] {
+                    ce = cudaLaunchCooperativeKernel((const void*)tail_levels_kernel<NW>, dim3(tail_grid), dim3(CTA), args, 0, s);
+                });
+                if (ce != cudaSuccess) return msbfs_fail(MSBFS_ERR_CUDA, "cooperative launch failed: %s", cudaGetErrorString(ce));
+                MSBFS_CUDA(cudaStreamSynchronize(s));
+                const int run = h->h_verdict->streak_levels;
+                levels += run - 1;
+                L.cur_level += run - 1;
+                levels_bu += run;
+                if (run % 2 == 0) { std::swap(a.cur, a.nxt); std::swap(a.cur_nz, a.nxt_nz); }
+                continue;
             } else {
                 ++levels_bu;
                 if (a.blk_multi > 0) {
@@ -1379,7 +1526,7 @@ template <int NW> void preload_kernels() {
                          (const void*)td_expand_kernel<NW, 2, 4>, (const void*)td_heavy_kernel<NW, 4>, (const void*)td_finalize_kernel<NW>,
                          (const void*)bu_thread_kernel<NW, 4>, (const void*)bu_thread_kernel<NW, 8>, (const void*)bu_segment_kernel<NW, 4>,
                          (const void*)bu_segment_kernel<NW, 8>, (const void*)bu_heavy_finalize_kernel<NW>, (const void*)count_kernel<NW, 0>,
-                         (const void*)td_streak_kernel<NW>, (const void*)init_batch_kernel, (const void*)epilogue_kernel,
+                         (const void*)td_streak_kernel<NW>, (const void*)tail_levels_kernel<NW>, (const void*)tail_list_kernel, (const void*)init_batch_kernel, (const void*)epilogue_kernel,
                          (const void*)store_sums_kernel};
     for (const void* f : fns) cudaFuncGetAttributes(&at, f);
     cudaGetLastError();
@@ -1559,6 +1706,7 @@ void msbfs_release_traversal(msbfs_handle* h) {
     cudaFree(h->d_ctrl); h->d_ctrl = nullptr;
     cudaFree(h->d_log); h->d_log = nullptr;
     if (h->h_verdict) { cudaFreeHost(h->h_verdict); h->h_verdict = nullptr; }
+    cudaFree(h->d_tail_list); h->d_tail_list = nullptr;
     h->nw_alloc = 0;
 }
 

@@ -17,8 +17,9 @@ OPTIONS = {
     "lm_ell": [1, 0],
     "col_width": [0, 4, 8],
     "alpha": [40, 4, 400],
+    "tail": [1, 0, 2, 2],
 }
-DEFAULTS = {"lanes": 0, "direction": 0, "reorder": 1, "count_missing": 1, "lane_major": -1, "lm_ell": 1, "col_width": 0, "alpha": 40}
+DEFAULTS = {"lanes": 0, "direction": 0, "reorder": 1, "count_missing": 1, "lane_major": -1, "lm_ell": 1, "col_width": 0, "alpha": 40, "tail": 1}
 
 
 def _graph(pkg, rng, shape):
