@@ -29,9 +29,13 @@
  *               segments of a row co-operate through hub_acc
  *   bu_heavy_finalize  hub_acc -> new frontier words of the long rows
  *   td_streak   persistent cooperative top-down loop for short-row (road-like) graphs
- *   count       positional popcount of the new frontier words (per-lane counts)
- *               with bit-sliced carry-save counters and warp bit-matrix transposes
+ *   tail_list / tail_levels   once few vertices are left unfinished: list them, then run every
+ *               remaining level bottom-up over the list in one cooperative launch
+ *   count       positional popcount (per-lane counts) with bit-sliced carry-save counters and
+ *               warp bit-matrix transposes: of the new frontier words, or, after a dense
+ *               bottom-up level, of the lanes the unfinished vertices still miss
  *   epilogue    F += (L+1) x counts, live-lane mask, direction for the next level
+ * Road-like graphs (every row short) go to the second engine in lane_major.cu instead.
  */
 #include "engine.h"
 
