@@ -215,3 +215,46 @@ def test_query_file_round_trip_fuzz(pkg, ob, tmp_path):
             assert o.tolist() == offs.tolist() and s.tolist() == src.tolist()
 
     check()
+
+
+def test_plan_shares_properties(pkg):
+    """msbfs_plan_shares on arbitrary weights / world sizes / widths: the run order is the stable
+    heaviest-first permutation, every group has exactly one owner in range, a batch (a run of
+    `lanes` consecutive groups of the order) is never split between ranks, and with measured
+    costs no rank is left idle while another holds two batches more than it needs to."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=150, deadline=None)
+    @given(st.lists(st.integers(0, 1 << 40), min_size=0, max_size=1500), st.integers(1, 9), st.sampled_from([0, 64, 128, 256, 512]),
+           st.booleans(), st.integers(0, 1 << 30))
+    def check(weights, world, lanes, with_costs, seed):
+        w = np.array(weights, dtype=np.int64)
+        k = int(w.size)
+        width = lanes or (pkg.lib().msbfs_plan_lanes(k, world) or 512)
+        costs = None
+        if with_costs and lanes and k:
+            nb = (k + lanes - 1) // lanes
+            costs = np.random.default_rng(seed).uniform(1.0, 30.0, size=nb)
+        share, out_lanes = pkg.plan_shares(w, world, lanes=lanes, batch_cost=costs)
+        assert len(share) == world
+        allg = np.concatenate(share) if k else np.zeros(0, np.int64)
+        assert sorted(allg.tolist()) == list(range(k))
+        if world == 1 or k == 0:
+            return
+        assert out_lanes in (64, 128, 256, 512) and (lanes == 0 or out_lanes == lanes)
+        order = np.lexsort((np.arange(k), -w))
+        pos = np.empty(k, np.int64); pos[order] = np.arange(k)
+        owner = np.empty(k, np.int64)
+        for r, sh in enumerate(share):
+            owner[sh] = r
+            assert np.all(np.diff(pos[sh]) > 0)            # a rank runs its groups in the global run order
+        for b in range(0, k, out_lanes):                    # a batch has one owner
+            assert len(set(owner[order[b:b + out_lanes]].tolist())) == 1
+        nb = (k + out_lanes - 1) // out_lanes
+        per_rank = np.bincount(owner[order[::out_lanes]], minlength=world)
+        if costs is None:
+            assert per_rank.max() - per_rank.min() <= 1     # snake order deals the batches out evenly
+        elif nb >= world:
+            assert per_rank.min() >= 1                      # longest-first never leaves a rank empty
+
+    check()
