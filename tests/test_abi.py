@@ -258,3 +258,22 @@ def test_plan_shares_properties(pkg):
             assert per_rank.min() >= 1                      # longest-first never leaves a rank empty
 
     check()
+
+
+def test_bench_sample_spread_is_a_permutation():
+    """bench.py's parity sample: group ids taken in turn from the first, a middle and the last 512-group
+    batch of the run order, then the rest — every group exactly once, heaviest batch first."""
+    import importlib
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    bench = importlib.import_module("bench")
+    rng = np.random.default_rng(5)
+    for k in (1, 17, 512, 513, 4096):
+        costs = rng.integers(0, 1000, size=k).astype(np.int64)
+        ids = bench.spread_over_run_order(costs)
+        assert sorted(ids.tolist()) == list(range(k))
+        order = np.lexsort((np.arange(k), -costs))
+        assert ids[0] == order[0]
+        if k > 1024:
+            nb = (k + 511) // 512
+            assert ids[1] == order[(nb // 2) * 512] and ids[2] == order[(nb - 1) * 512]
