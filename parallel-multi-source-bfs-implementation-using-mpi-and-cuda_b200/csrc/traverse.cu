@@ -386,9 +386,11 @@ struct TileBits {
  * chains are in flight; a densely touched tile is walked block by block, lane = vertex. */
 template <int NW>
 __device__ __forceinline__ void td_finalize_vertex(const TravArgs& a, int v, const LW<NW>& active, ull& full_acc) {
+    /* both loads first: a store in between would keep the second load from being issued early */
     const LW<NW> x = lw_load<NW>(a.acc, v);
+    const LW<NW> vis = lw_load<NW>(a.visited, v);
+    const LW<NW> nv = lw_or(vis, x);
     lw_store<NW>(a.acc, v, lw_zero<NW>());
-    const LW<NW> nv = lw_or(lw_load<NW>(a.visited, v), x);
     lw_store<NW>(a.visited, v, nv);
     lw_store<NW>(a.nxt, v, x);
     if (lw_covers(nv, active)) {
